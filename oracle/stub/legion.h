@@ -1,0 +1,134 @@
+// TEST INFRASTRUCTURE ONLY -- minimal stand-in for Legion's "legion.h".
+//
+// The reference's hot-path numerics (/root/reference/src/prometeo_*.{hpp,inl},
+// Mixtures/*, Utils/*) are header-style C++ that only *name* a handful of
+// Legion types.  This stub provides exactly those names so that the reference
+// sources can be compiled IN PLACE (never copied) into oracle/_ref/ and driven
+// over raw host arrays by oracle/ref_driver.cc.  It contains no HTR code.
+// Surface list: SURVEY.md section 8(c).
+#ifndef HTR_ORACLE_STUB_LEGION_H
+#define HTR_ORACLE_STUB_LEGION_H
+
+#include <cstdint>
+#include <cstddef>
+#include <cstring>
+#include <vector>
+#include <cassert>
+#include <cmath>
+#include <algorithm>
+
+enum legion_privilege_mode_stub { READ_ONLY = 1, READ_WRITE = 7, WRITE_ONLY = 0x10000002, WRITE_DISCARD = 0x10000002, REDUCE = 8 };
+
+namespace Realm {
+   template<typename FT, int N, typename T> struct AffineAccessor {};
+}
+
+namespace Legion {
+   typedef long long coord_t;
+   typedef unsigned int FieldID;
+   typedef unsigned int LayoutConstraintID;
+   typedef unsigned int TaskID;
+   typedef void* Context;
+
+   template<int N, typename T = coord_t> struct Point;
+   template<typename T> struct Point<1, T> {
+      T x;
+      Point() : x(0) {}
+      Point(T x_) : x(x_) {}
+      operator T() const { return x; }
+      T operator[](int) const { return x; }
+   };
+   template<typename T> struct Point<3, T> {
+      T x, y, z;
+      Point() : x(0), y(0), z(0) {}
+      Point(T x_, T y_, T z_) : x(x_), y(y_), z(z_) {}
+      T operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+   };
+   template<int N, typename T = coord_t> struct Rect {
+      Point<N, T> lo, hi;
+      Rect() {}
+      Rect(const Point<N, T> &l, const Point<N, T> &h) : lo(l), hi(h) {}
+      size_t volume() const;
+   };
+   template<> inline size_t Rect<3, coord_t>::volume() const {
+      return size_t(hi.x - lo.x + 1)*size_t(hi.y - lo.y + 1)*size_t(hi.z - lo.z + 1);
+   }
+   template<> inline size_t Rect<1, coord_t>::volume() const { return size_t(hi.x - lo.x + 1); }
+
+   struct Domain {
+      Rect<3> r3; Rect<1> r1;
+      Domain() {}
+      Domain(const Rect<3> &r) : r3(r) {}
+      operator Rect<3>() const { return r3; }
+      operator Rect<1>() const { return r1; }
+   };
+
+   struct IndexSpace { Rect<3> bounds; };
+   struct FieldSpace { unsigned id; };
+   struct LogicalRegion {
+      unsigned tree_id; unsigned long long index_space_id; unsigned is_tid; unsigned type_tag; unsigned field_space_id;
+      IndexSpace get_index_space() const { return IndexSpace(); }
+   };
+   struct PhysicalRegion {
+      LogicalRegion get_logical_region() const { return LogicalRegion(); }
+   };
+   struct Future {
+      double v;
+      template<typename T> T get_result() const { return T(v); }
+   };
+   struct Task {
+      void *args; size_t arglen; void *local_args; size_t local_arglen;
+      std::vector<Future> futures;
+   };
+   struct Processor { enum Kind { NO_KIND, TOC_PROC, LOC_PROC, UTIL_PROC, IO_PROC, PROC_GROUP, PROC_SET, OMP_PROC, PY_PROC }; };
+   struct Memory { enum Kind { NO_MEMKIND, GLOBAL_MEM, SYSTEM_MEM, REGDMA_MEM, SOCKET_MEM, Z_COPY_MEM, GPU_FB_MEM }; };
+   struct ProcessorConstraint { ProcessorConstraint(Processor::Kind) {} };
+   struct OrderingConstraint { template<typename V> OrderingConstraint(const V&, bool) {} };
+   struct LayoutConstraintRegistrar {
+      LayoutConstraintRegistrar() {}
+      template<typename A, typename B> LayoutConstraintRegistrar(A, B) {}
+      template<typename C> LayoutConstraintRegistrar& add_constraint(const C&) { return *this; }
+   };
+   struct TaskVariantRegistrar {
+      TaskVariantRegistrar(TaskID, const char*) {}
+      template<typename C> TaskVariantRegistrar& add_constraint(const C&) { return *this; }
+      TaskVariantRegistrar& add_layout_constraint_set(unsigned, LayoutConstraintID) { return *this; }
+      void set_leaf(bool = true) {}
+   };
+   struct Runtime {
+      Domain get_index_space_domain(Context, const IndexSpace &is) { return Domain(is.bounds); }
+      template<void (*F)(const Task*, const std::vector<PhysicalRegion>&, Context, Runtime*)>
+      static void preregister_task_variant(const TaskVariantRegistrar&, const char*) {}
+      template<typename R, R (*F)(const Task*, const std::vector<PhysicalRegion>&, Context, Runtime*)>
+      static void preregister_task_variant(const TaskVariantRegistrar&, const char*) {}
+      static LayoutConstraintID preregister_layout(const LayoutConstraintRegistrar&) { return 0; }
+   };
+   template<typename T> class SumReduction {};
+   template<typename T> struct DeferredValue { T v; DeferredValue(T x = T()) : v(x) {} };
+   template<typename T, int N> struct DeferredBuffer {};
+   template<int N> struct RectInDomainIterator {};
+
+   // Accessor over a raw strided host array (byte strides, like Realm::AffineAccessor).
+   template<int PRIV, typename FT, int N, typename T = coord_t, typename A = Realm::AffineAccessor<FT, N, T> >
+   struct FieldAccessor;
+   template<int PRIV, typename FT, typename T, typename A>
+   struct FieldAccessor<PRIV, FT, 3, T, A> {
+      char *base; coord_t sx, sy, sz;   // base addresses global point (0,0,0)
+      FieldAccessor() : base(0), sx(0), sy(0), sz(0) {}
+      FieldAccessor(const PhysicalRegion&, FieldID) : base(0), sx(0), sy(0), sz(0) {}
+      FieldAccessor(void *b, coord_t sx_, coord_t sy_, coord_t sz_) : base((char*)b), sx(sx_), sy(sy_), sz(sz_) {}
+      FT& operator[](const Point<3, T> &p) const { return *(FT*)(base + p.x*sx + p.y*sy + p.z*sz); }
+   };
+   template<int PRIV, typename FT, typename T, typename A>
+   struct FieldAccessor<PRIV, FT, 1, T, A> {
+      char *base; coord_t sx;
+      FieldAccessor() : base(0), sx(0) {}
+      FieldAccessor(const PhysicalRegion&, FieldID) : base(0), sx(0) {}
+      FieldAccessor(void *b, coord_t sx_) : base((char*)b), sx(sx_) {}
+      FT& operator[](const Point<1, T> &p) const { return *(FT*)(base + p.x*sx); }
+      FT& operator[](coord_t i) const { return *(FT*)(base + i*sx); }
+   };
+   template<typename REDOP, bool EXCLUSIVE, int N, typename T = coord_t, typename A = void>
+   struct ReductionAccessor {};
+}
+#endif
