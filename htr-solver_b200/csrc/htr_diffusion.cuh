@@ -1,0 +1,102 @@
+// Diffusion face flux at i+1/2 along `dir` (viscous stress, Fourier + species-enthalpy heat
+// flux, Fickian species flux with correction velocity), 2nd-order staggered.
+// Arithmetic of src/prometeo_rhs.inl:1058-1215 (GetSigma, GetDiffusionFlux); each face is
+// evaluated independently: the two transverse velocity gradients the reference carries
+// from face to face (vGrad[0] <- vGrad[1]) are simply recomputed at p and p+1.
+#pragma once
+#include "htr_access.cuh"
+#include "htr_mix.cuh"
+#include "htr_stencil.cuh"
+
+namespace htr {
+
+// d(velocity)/d(xi_D) at cell q, all three components
+template<int D>
+HTR_DEV void velocityDeriv(double *g, const htr_fluid &f, const Pt &q, const htr_rect &B) {
+   const int t = ld<int>(nTypeOf<D>(f), q);
+   const double m = ld<double>(m_dOf<D>(f), q);
+   const Pt qm = shift<D>(q, offM1(t), B);
+   const Pt qp = shift<D>(q, offP1(t), B);
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++)
+      g[i] = getDeriv(t, ldc<double>(f.velocity, qm, i), ldc<double>(f.velocity, q, i), ldc<double>(f.velocity, qp, i), m);
+}
+
+template<int dir>
+HTR_DEV void diffusionFaceFlux(double *Flux, const htr_fluid &f, const Pt &p, const htr_rect &B) {
+   constexpr int D1 = T1(dir), D2 = T2(dir);
+   const int t = ld<int>(nTypeOf<dir>(f), p);
+   const double m_s = ld<double>(m_sOf<dir>(f), p);
+   const Pt pp1 = shift<dir>(p, 1, B);
+
+   double g1[2][3], g2[2][3];     // transverse gradients at p and p+1
+   velocityDeriv<D1>(g1[0], f, p, B);   velocityDeriv<D2>(g2[0], f, p, B);
+   velocityDeriv<D1>(g1[1], f, pp1, B); velocityDeriv<D2>(g2[1], f, pp1, B);
+
+   double Xp[nSpec], Xq[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) { Xp[i] = ldc<double>(f.MolarFracs, p, i); Xq[i] = ldc<double>(f.MolarFracs, pp1, i); }
+
+   const double rho_s = Interp2Staggered(t, ld<double>(f.rho, p), ld<double>(f.rho, pp1));
+   const double iMixW_s = 1.0/Interp2Staggered(t, mix::GetMolarWeightFromXi(Xp), mix::GetMolarWeightFromXi(Xq));
+   const double Tp = ld<double>(f.temperature, p), Tq = ld<double>(f.temperature, pp1);
+   const double T_s = Interp2Staggered(t, Tp, Tq);
+   double heatFlux = Interp2Staggered(t, ld<double>(f.lam, p), ld<double>(f.lam, pp1))*m_s*(Tp - Tq);
+
+   double hi[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) hi[i] = mix::GetSpeciesEnthalpy(i, T_s);
+
+   double ViCorr = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      const double YiVi = Interp2Staggered(t, ldc<double>(f.Di, p, i), ldc<double>(f.Di, pp1, i))*
+                          m_s*(Xp[i] - Xq[i])*mix::GetSpeciesMolarWeight(i)*iMixW_s;
+      Flux[i] = -rho_s*YiVi;
+      heatFlux += rho_s*YiVi*hi[i];
+      ViCorr += YiVi;
+   }
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      const double rhoYiViCorr = Interp2Staggered(t, ldc<double>(f.Conserved, p, i), ldc<double>(f.Conserved, pp1, i))*ViCorr;
+      Flux[i] += rhoYiViCorr;
+      heatFlux -= rhoYiViCorr*hi[i];
+   }
+
+   // viscous stress on the face
+   double up[3], uq[3];
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) { up[i] = ldc<double>(f.velocity, p, i); uq[i] = ldc<double>(f.velocity, pp1, i); }
+   const double mu_s = Interp2Staggered(t, ld<double>(f.mu, p), ld<double>(f.mu, pp1));
+   double dN[3];                       // d(u,v,w)/d(normal) on the face
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) dN[i] = m_s*(uq[i] - up[i]);
+   // transverse derivatives interpolated to the face: d u_a / d x_b
+   #define HTR_TG(g, a) Interp2Staggered(t, g[0][a], g[1][a])
+   double sigma[3];
+   if (dir == 0) {
+      const double dVdY = HTR_TG(g1, 1), dUdY = HTR_TG(g1, 0), dUdZ = HTR_TG(g2, 0), dWdZ = HTR_TG(g2, 2);
+      sigma[0] = mu_s*(4*dN[0] - 2*dVdY - 2*dWdZ)/3;
+      sigma[1] = mu_s*(dN[1] + dUdY);
+      sigma[2] = mu_s*(dN[2] + dUdZ);
+   } else if (dir == 1) {
+      const double dUdX = HTR_TG(g1, 0), dVdX = HTR_TG(g1, 1), dVdZ = HTR_TG(g2, 1), dWdZ = HTR_TG(g2, 2);
+      sigma[0] = mu_s*(dN[0] + dVdX);
+      sigma[1] = mu_s*(4*dN[1] - 2*dUdX - 2*dWdZ)/3;
+      sigma[2] = mu_s*(dN[2] + dVdZ);
+   } else {
+      const double dUdX = HTR_TG(g1, 0), dWdX = HTR_TG(g1, 2), dVdY = HTR_TG(g2, 1), dWdY = HTR_TG(g2, 2);
+      sigma[0] = mu_s*(dN[0] + dWdX);
+      sigma[1] = mu_s*(dN[1] + dWdY);
+      sigma[2] = mu_s*(4*dN[2] - 2*dUdX - 2*dVdY)/3;
+   }
+   #undef HTR_TG
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) Flux[irU + i] = sigma[i];
+   double uSigma = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) uSigma += Interp2Staggered(t, up[i], uq[i])*sigma[i];
+   Flux[irE] = (uSigma - heatFlux);
+}
+
+} // namespace htr

@@ -1,0 +1,481 @@
+// Kernels and C ABI (include/htr_b200.h) of the B200-native HTR right-hand-side engine.
+// Built once per mixture for sm_100a (see htr-solver_b200/build.py).
+//
+// Kernel shapes (x is the unit-stride direction of every field):
+//   flux kernels   one thread per FACE of a (BX,BY,BZ) block of faces; the face fluxes are
+//                  exchanged through shared memory and each thread then updates the cell on
+//                  the minus side of its face:  Conserved_t[p] += m[p]*(F[p+1/2] - F[p-1/2])
+//                  (src/prometeo_rhs.inl:884, :968, :1047, :1277).  A block of B faces along the
+//                  flux direction updates B-1 cells.
+//   point kernels  one thread per cell, x fastest.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include "htr_euler.cuh"
+#include "htr_diffusion.cuh"
+#include "htr_pointwise.cuh"
+
+namespace htr {
+
+// ---------------------------------------------------------------------------------------------
+// flux kernels
+// ---------------------------------------------------------------------------------------------
+enum { FLUX_EULER = 0, FLUX_DIFFUSION = 1 };
+
+struct EulerParams { double RK0, RK1, dt; };
+
+template<int dir> struct FaceBlock;            // faces per block in (x, y, z)
+template<> struct FaceBlock<0> { static constexpr int X = 64, Y = 4, Z = 1; };
+template<> struct FaceBlock<1> { static constexpr int X = 32, Y = 8, Z = 1; };
+template<> struct FaceBlock<2> { static constexpr int X = 32, Y = 1, Z = 8; };
+
+template<int dir, int SCHEME>
+HTR_DEV void eulerFace(double *Flux, const htr_fluid &f, const Pt &p, int t, const htr_rect &B, const EulerParams &ep) {
+   if (SCHEME == HTR_SCHEME_SKEWSYMMETRIC) {
+      kgFaceFlux<dir>(Flux, f, p, t, B);
+      return;
+   }
+   double lim_f = 0.0;
+   if (nSpec > 1)
+      lim_f = ep.dt*(ld<double>(m_eOf<dir>(f), p) + ld<double>(m_eOf<dir>(f), shift<dir>(p, offP1(t), B)));
+   if (SCHEME == HTR_SCHEME_HYBRID) {
+      const htr_acc &ss = sensorOf<dir>(f);
+      const bool smooth = ld<uint8_t>(ss, shift<dir>(p, offM1(t), B)) && ld<uint8_t>(ss, p) &&
+                          ld<uint8_t>(ss, shift<dir>(p, offP1(t), B));
+      if (smooth) kgFaceFlux<dir>(Flux, f, p, t, B);
+      else        tenoFaceFlux<dir, OP_TENO>(Flux, f, p, t, B, ep.RK0, ep.RK1, lim_f);
+   }
+   else if (SCHEME == HTR_SCHEME_TENO)    tenoFaceFlux<dir, OP_TENO>(Flux, f, p, t, B, ep.RK0, ep.RK1, lim_f);
+   else if (SCHEME == HTR_SCHEME_TENOA)   tenoFaceFlux<dir, OP_TENOA>(Flux, f, p, t, B, ep.RK0, ep.RK1, lim_f);
+   else if (SCHEME == HTR_SCHEME_TENOLAD) tenoFaceFlux<dir, OP_TENOLAD>(Flux, f, p, t, B, ep.RK0, ep.RK1, lim_f);
+}
+
+// KIND = FLUX_EULER (SCHEME selects the reconstruction) or FLUX_DIFFUSION
+template<int dir, int KIND, int SCHEME>
+__global__ void __launch_bounds__(256)
+flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep) {
+   using FB = FaceBlock<dir>;
+   constexpr int NT = FB::X*FB::Y*FB::Z;
+   __shared__ double sF[nEq][NT];
+
+   const int tid = threadIdx.x + FB::X*(threadIdx.y + FB::Y*threadIdx.z);
+   const int fd = (dir == 0) ? threadIdx.x : ((dir == 1) ? threadIdx.y : threadIdx.z);   // face index along dir
+   constexpr int CX = FB::X - (dir == 0), CY = FB::Y - (dir == 1), CZ = FB::Z - (dir == 2); // cells per block
+   // cell on the minus side of this thread's face; fd == 0 is the face below the block's first cell
+   Pt c;
+   c.x = tile.lo[0] + (int64_t)blockIdx.x*CX + threadIdx.x - (dir == 0);
+   c.y = tile.lo[1] + (int64_t)blockIdx.y*CY + threadIdx.y - (dir == 1);
+   c.z = tile.lo[2] + (int64_t)blockIdx.z*CZ + threadIdx.z - (dir == 2);
+   const bool inCross = (dir == 0 || c.x <= tile.hi[0]) && (dir == 1 || c.y <= tile.hi[1]) && (dir == 2 || c.z <= tile.hi[2]);
+   const int64_t cd = (dir == 0) ? c.x : ((dir == 1) ? c.y : c.z);
+   const bool active = inCross && (cd <= tile.hi[dir]);
+
+   if (active) {
+      Pt p = c;
+      if (fd == 0) {
+         // first minus face of the block: the face owned by the neighbour below the first cell
+         Pt p0 = c;
+         ((dir == 0) ? p0.x : ((dir == 1) ? p0.y : p0.z)) += 1;
+         p = shift<dir>(p0, offM1(ld<int>(nTypeOf<dir>(f), p0)), B);
+      }
+      const int t = ld<int>(nTypeOf<dir>(f), p);
+      double Flux[nEq];
+      if (KIND == FLUX_EULER) eulerFace<dir, SCHEME>(Flux, f, p, t, B, ep);
+      else                    diffusionFaceFlux<dir>(Flux, f, p, B);
+      HTR_UNROLL
+      for (int i = 0; i < nEq; i++) sF[i][tid] = Flux[i];
+   }
+   __syncthreads();
+   if (active && fd > 0) {
+      constexpr int below = (dir == 0) ? 1 : ((dir == 1) ? FB::X : FB::X*FB::Y);
+      const double m = ld<double>((KIND == FLUX_EULER) ? m_eOf<dir>(f) : m_dOf<dir>(f), c);
+      double *Ct = at<double>(f.Conserved_t, c);
+      HTR_UNROLL
+      for (int i = 0; i < nEq; i++) Ct[i] += m*(sF[i][tid] - sF[i][tid - below]);
+   }
+}
+
+template<int dir, int KIND, int SCHEME>
+static cudaError_t launchFlux(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep, cudaStream_t st) {
+   using FB = FaceBlock<dir>;
+   const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
+   if (n[0] <= 0 || n[1] <= 0 || n[2] <= 0) return cudaSuccess;
+   const int C[3] = {FB::X - (dir == 0), FB::Y - (dir == 1), FB::Z - (dir == 2)};
+   dim3 grid((unsigned)((n[0] + C[0] - 1)/C[0]), (unsigned)((n[1] + C[1] - 1)/C[1]), (unsigned)((n[2] + C[2] - 1)/C[2]));
+   dim3 block(FB::X, FB::Y, FB::Z);
+   flux_divergence_kernel<dir, KIND, SCHEME><<<grid, block, 0, st>>>(f, tile, B, ep);
+   return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------------------------
+// point kernels
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool cellOf(Pt &p, const htr_rect &tile) {
+   const int64_t nx = tile.hi[0] - tile.lo[0] + 1, ny = tile.hi[1] - tile.lo[1] + 1, nz = tile.hi[2] - tile.lo[2] + 1;
+   const int64_t g = (int64_t)blockIdx.x*blockDim.x + threadIdx.x;
+   if (g >= nx*ny*nz) return false;
+   p.x = tile.lo[0] + g % nx;
+   p.y = tile.lo[1] + (g/nx) % ny;
+   p.z = tile.lo[2] + g/(nx*ny);
+   return true;
+}
+
+__global__ void __launch_bounds__(128) ducros_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const double eps) {
+   Pt p; if (!cellOf(p, tile)) return;
+   *at<double>(f.DucrosSensor, p) = ducrosSensor(f, p, B, eps);
+}
+
+template<int dir>
+__global__ void __launch_bounds__(128) shock_sensor_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B) {
+   Pt p; if (!cellOf(p, tile)) return;
+   *at<uint8_t>(sensorOf<dir>(f), p) = shockSensor<dir>(f, p, B) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(128) chem_source_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double Yi[nSpec], w[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Yi[i] = ldc<double>(f.MassFracs, p, i);
+   mix::GetProductionRates(w, ld<double>(f.rho, p), ld<double>(f.pressure, p), ld<double>(f.temperature, p), Yi);
+   double *Ct = at<double>(f.Conserved_t, p);
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Ct[i] += w[i];
+}
+
+__device__ int d_chem_failures;
+
+__global__ void __launch_bounds__(64) update_chemistry_kernel(const htr_fluid f, const htr_rect tile, const double dt) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double S[nEq], x[nEq];
+   const double *Ct = at<const double>(f.Conserved_t, p);
+   double *Cto = at<double>(f.Conserved_t_old, p);
+   double *C = at<double>(f.Conserved, p);
+   for (int i = 0; i < nEq; i++) { S[i] = Ct[i]; Cto[i] = S[i]; x[i] = C[i]; }
+   ChemProblem prob; prob.S = S; prob.T = *at<double>(f.temperature, p);
+   if (!rosenbrockSolve<nEq>(prob, x, dt, dt)) atomicAdd(&d_chem_failures, 1);
+   for (int i = 0; i < nEq; i++) C[i] = x[i];
+   *at<double>(f.temperature, p) = prob.T;
+}
+
+__global__ void __launch_bounds__(128) primitive_from_conserved_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double U[nEq], rho, Yi[nSpec], MixW, u[3], P;
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) U[i] = ldc<double>(f.Conserved, p, i);
+   double T = *at<double>(f.temperature, p);
+   primitivesFromConserved(U, rho, Yi, MixW, u, T, P);
+   double Xi[nSpec];
+   mix::GetMolarFractions(Xi, MixW, Yi);
+   double *X = at<double>(f.MolarFracs, p), *v = at<double>(f.velocity, p);
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) X[i] = Xi[i];
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) v[i] = u[i];
+   *at<double>(f.temperature, p) = T;
+   *at<double>(f.pressure, p) = P;
+}
+
+__global__ void __launch_bounds__(128) properties_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double Xi[nSpec], Yi[nSpec], Di[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Xi[i] = ldc<double>(f.MolarFracs, p, i);
+   const double P = ld<double>(f.pressure, p), T = ld<double>(f.temperature, p);
+   const double MixW = mix::GetMolarWeightFromXi(Xi);
+   *at<double>(f.rho, p) = mix::GetRho(P, T, MixW);
+   *at<double>(f.mu, p) = mix::GetViscosity(T, Xi);
+   *at<double>(f.lam, p) = mix::GetHeatConductivity(T, Xi);
+   mix::GetDiffusivity(Di, P, T, MixW, Xi);
+   mix::GetMassFractions(Yi, MixW, Xi);
+   const double gamma = mix::GetGamma(T, MixW, Yi);
+   *at<double>(f.SoS, p) = mix::GetSpeedOfSound(T, gamma, MixW);
+   double *oD = at<double>(f.Di, p), *oY = at<double>(f.MassFracs, p);
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) { oD[i] = Di[i]; oY[i] = Yi[i]; }
+}
+
+__global__ void __launch_bounds__(128) conserved_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double Yi[nSpec], u[3];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Yi[i] = ldc<double>(f.MassFracs, p, i);
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) u[i] = ldc<double>(f.velocity, p, i);
+   const double rho = ld<double>(f.rho, p);
+   double *C = at<double>(f.Conserved, p);
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) C[i] = rho*Yi[i];
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) C[i + irU] = rho*u[i];
+   C[irE] = rho*(0.5*mod2(u) + mix::GetInternalEnergy(ld<double>(f.temperature, p), Yi));
+}
+
+__global__ void __launch_bounds__(128) zero_rhs_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double *Ct = at<double>(f.Conserved_t, p);
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) Ct[i] = 0.0;
+}
+
+// max over the tile: warp shuffle, one shared slot per warp, then one atomic per block on the
+// bit pattern (radii are >= 0, so integer order == floating order; max is order independent)
+__global__ void __launch_bounds__(256) spectral_radius_kernel(const htr_fluid f, const htr_rect tile, double *result) {
+   Pt p;
+   double r = 0.0;
+   if (cellOf(p, tile)) r = spectralRadius(f, p);
+   HTR_UNROLL
+   for (int o = 16; o > 0; o >>= 1) r = fmax(r, __shfl_xor_sync(0xffffffffu, r, o));
+   __shared__ double sm[8];
+   if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = r;
+   __syncthreads();
+   if (threadIdx.x < 32) {
+      r = (threadIdx.x < (blockDim.x >> 5)) ? sm[threadIdx.x] : 0.0;
+      HTR_UNROLL
+      for (int o = 4; o > 0; o >>= 1) r = fmax(r, __shfl_xor_sync(0xffffffffu, r, o));
+      if (threadIdx.x == 0) atomicMax(reinterpret_cast<unsigned long long*>(result), (unsigned long long)__double_as_longlong(r));
+   }
+}
+
+} // namespace htr
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+using namespace htr;
+
+#if HTR_MULTICOMP
+#if defined(HTR_MIX_AirMix)
+#include "generated/AirMix_tables.inc"
+#define HTR_TABLES htr_AirMix_tables
+#define HTR_TABLE_BYTES HTR_AIRMIX_TABLE_BYTES
+#endif
+#endif
+
+static bool g_mix_loaded = false;
+
+static inline int cuerr(cudaError_t e) { return e == cudaSuccess ? HTR_OK : 1000 + (int)e; }
+static inline bool rectEmpty(const htr_rect &r) { return r.hi[0] < r.lo[0] || r.hi[1] < r.lo[1] || r.hi[2] < r.lo[2]; }
+static inline unsigned blocksFor(const htr_rect &t, int threads) {
+   const int64_t n = (t.hi[0] - t.lo[0] + 1)*(t.hi[1] - t.lo[1] + 1)*(t.hi[2] - t.lo[2] + 1);
+   return (unsigned)((n + threads - 1)/threads);
+}
+
+template<int KIND, int SCHEME>
+static int dispatchDir(int dir, const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep, cudaStream_t st) {
+   switch (dir) {
+   case 0: return cuerr(launchFlux<0, KIND, SCHEME>(f, tile, B, ep, st));
+   case 1: return cuerr(launchFlux<1, KIND, SCHEME>(f, tile, B, ep, st));
+   case 2: return cuerr(launchFlux<2, KIND, SCHEME>(f, tile, B, ep, st));
+   }
+   return HTR_EINVAL;
+}
+
+extern "C" {
+
+int htr_nspec(void) { return nSpec; }
+int htr_neq(void) { return nEq; }
+const char *htr_mixture_name(void) { return HTR_MIX_NAME; }
+int htr_sizeof_mix(void) { return (int)sizeof(MixData); }
+const char *htr_build_info(void) {
+   return "htr_b200 " HTR_MIX_NAME " sm_100a"
+#ifdef HTR_EXACT_POW
+      " exact-pow"
+#endif
+#ifdef HTR_FMAD_OFF
+      " fmad=false"
+#endif
+      ;
+}
+
+int htr_mix_init_constprop(void *out, double gasConstant, double gamma, double prandtl,
+                           int visc_model, double p0, double p1, double p2) {
+#if HTR_MULTICOMP
+   (void)out; (void)gasConstant; (void)gamma; (void)prandtl; (void)visc_model; (void)p0; (void)p1; (void)p2;
+   return HTR_EMIXTYPE;
+#else
+   if (!out || visc_model < 0 || visc_model > 2) return HTR_EINVAL;
+   MixData m;
+   memset(&m, 0, sizeof(m));
+   m.R = gasConstant; m.gamma = gamma; m.viscosityModel = visc_model; m.Prandtl = prandtl;
+   if (visc_model == 0) m.constantVisc = p0;
+   else if (visc_model == 1) { m.powerlawViscRef = p0; m.powerlawTempRef = p1; }
+   else { m.sutherlandViscRef = p0; m.sutherlandTempRef = p1; m.sutherlandSRef = p2; }
+   memcpy(out, &m, sizeof(m));
+   return HTR_OK;
+#endif
+}
+
+int htr_mix_init_multicomp(void *out, double LRef, double PRef, double TRef,
+                           int n, const char *names, const double *molarFracs) {
+#if !HTR_MULTICOMP
+   (void)out; (void)LRef; (void)PRef; (void)TRef; (void)n; (void)names; (void)molarFracs;
+   return HTR_EMIXTYPE;
+#else
+   if (!out || !(PRef > 0) || !(LRef > 0) || !(TRef > 0) || n < 0 || (n > 0 && (!names || !molarFracs))) return HTR_EINVAL;
+   static_assert(HTR_TABLE_BYTES == offsetof(MixData, PRef), "species/reaction tables must end where PRef starts");
+   MixData m;
+   memset(&m, 0, sizeof(m));
+   memcpy(&m, HTR_TABLES, HTR_TABLE_BYTES);
+   // reference quantities (src/Mixtures/MultiComponent.inl:438-488)
+   m.PRef = PRef; m.TRef = TRef;
+   for (int i = 0; i < nSpec; i++) m.XiRef[i] = 1.0e-60;
+   double check = 0.0;
+   for (int k = 0; k < n; k++) {
+      char nm[11]; memcpy(nm, names + 10*k, 10); nm[10] = 0;
+      int is = -1;
+      for (int i = 0; i < nSpec; i++) if (strcmp(m.species[i].Name, nm) == 0) { is = i; break; }
+      if (is < 0) return HTR_EINVAL;
+      m.XiRef[is] = molarFracs[k];
+      check += molarFracs[k];
+   }
+   if (!(fabs(check - 1.0) < 1e-3)) return HTR_EINVAL;
+   double W = 0.0;
+   for (int i = 0; i < nSpec; i++) W += m.XiRef[i]*m.species[i].W;
+   m.MixWRef = W;
+   m.iMixWRef = 1.0/m.MixWRef;
+   m.rhoRef = PRef*m.MixWRef/(RGAS*TRef);
+   m.ieRef = m.rhoRef/PRef;
+   m.iuRef = sqrt(m.ieRef);
+   m.iCpRef = m.MixWRef/RGAS;
+   m.imuRef = 1.0/(LRef*sqrt(PRef*m.rhoRef));
+   m.ilamRef = m.MixWRef/(LRef*sqrt(PRef*m.rhoRef)*RGAS);
+   m.iDiRef = sqrt(m.rhoRef/PRef)/(LRef);
+   m.iwiRef = LRef/sqrt(m.rhoRef*PRef);
+   m.iKiRef = sqrt(PRef/m.rhoRef)*m.MixWRef/(Na*LRef*eCrg);
+   m.Eps0 = m.MixWRef/(m.rhoRef*Na*eCrg*LRef);
+   m.Eps0 = eps_0*PRef*m.Eps0*m.Eps0;
+   m.TMax = 1e20; m.TMin = 0.0;
+   for (int i = 0; i < nSpec; i++) {
+      m.TMax = fmin(m.TMax, m.species[i].cp.TMax/TRef);
+      m.TMin = fmax(m.TMin, m.species[i].cp.TMin/TRef);
+   }
+   memcpy(out, &m, sizeof(m));
+   return HTR_OK;
+#endif
+}
+
+int htr_set_mixture(const void *mix, size_t bytes) {
+   if (!mix || bytes != sizeof(MixData)) return HTR_EINVAL;
+   cudaError_t e = cudaMemcpyToSymbol(c_mix, mix, sizeof(MixData));
+   if (e == cudaSuccess) g_mix_loaded = true;
+   return cuerr(e);
+}
+
+#define HTR_CHECK_COMMON(f, tile) \
+   if (!(f) || !(tile)) return HTR_EINVAL; \
+   if (!g_mix_loaded) return HTR_ENOMIX; \
+   if (rectEmpty(*(tile))) return HTR_OK;
+
+int htr_euler_flux(int scheme, int dir, const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds,
+                   double RK0, double RK1, double deltaTime, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds || dir < 0 || dir > 2) return HTR_EINVAL;
+   const EulerParams ep = {RK0, RK1, deltaTime};
+   cudaStream_t st = (cudaStream_t)stream;
+   switch (scheme) {
+   case HTR_SCHEME_HYBRID:        return dispatchDir<FLUX_EULER, HTR_SCHEME_HYBRID>(dir, *f, *tile, *bounds, ep, st);
+   case HTR_SCHEME_TENO:          return dispatchDir<FLUX_EULER, HTR_SCHEME_TENO>(dir, *f, *tile, *bounds, ep, st);
+   case HTR_SCHEME_TENOA:         return dispatchDir<FLUX_EULER, HTR_SCHEME_TENOA>(dir, *f, *tile, *bounds, ep, st);
+   case HTR_SCHEME_TENOLAD:       return dispatchDir<FLUX_EULER, HTR_SCHEME_TENOLAD>(dir, *f, *tile, *bounds, ep, st);
+   case HTR_SCHEME_SKEWSYMMETRIC: return dispatchDir<FLUX_EULER, HTR_SCHEME_SKEWSYMMETRIC>(dir, *f, *tile, *bounds, ep, st);
+   }
+   return HTR_EINVAL;
+}
+
+int htr_diffusion_flux(int dir, const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds || dir < 0 || dir > 2) return HTR_EINVAL;
+   const EulerParams ep = {0, 0, 0};
+   return dispatchDir<FLUX_DIFFUSION, 0>(dir, *f, *tile, *bounds, ep, (cudaStream_t)stream);
+}
+
+int htr_ducros_sensor(const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds, double vorticityScale, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds) return HTR_EINVAL;
+   const double eps = fmax(vorticityScale*vorticityScale, 1e-6);      // src/prometeo_sensor.cc:62
+   ducros_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, *bounds, eps);
+   return cuerr(cudaGetLastError());
+}
+
+int htr_shock_sensor(int dir, const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds || dir < 0 || dir > 2) return HTR_EINVAL;
+   cudaStream_t st = (cudaStream_t)stream;
+   const unsigned nb = blocksFor(*tile, 128);
+   if (dir == 0) shock_sensor_kernel<0><<<nb, 128, 0, st>>>(*f, *tile, *bounds);
+   else if (dir == 1) shock_sensor_kernel<1><<<nb, 128, 0, st>>>(*f, *tile, *bounds);
+   else shock_sensor_kernel<2><<<nb, 128, 0, st>>>(*f, *tile, *bounds);
+   return cuerr(cudaGetLastError());
+}
+
+int htr_add_chemistry_sources(const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   chem_source_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   return cuerr(cudaGetLastError());
+}
+
+int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double dt, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   update_chemistry_kernel<<<blocksFor(*tile, 64), 64, 0, (cudaStream_t)stream>>>(*f, *tile, dt);
+   return cuerr(cudaGetLastError());
+}
+
+/* number of cells whose implicit integration hit the iteration caps since the last call
+ * (the reference asserts, src/Utils/math_utils.hpp:233,240); synchronises the device */
+int htr_chemistry_failures(void) {
+   int n = 0, zero = 0;
+   if (cudaMemcpyFromSymbol(&n, d_chem_failures, sizeof(int)) != cudaSuccess) return -1;
+   cudaMemcpyToSymbol(d_chem_failures, &zero, sizeof(int));
+   return n;
+}
+
+int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   primitive_from_conserved_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   return cuerr(cudaGetLastError());
+}
+int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   properties_from_primitive_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   return cuerr(cudaGetLastError());
+}
+int htr_update_conserved_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   conserved_from_primitive_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   return cuerr(cudaGetLastError());
+}
+
+int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_result, void *stream) {
+   if (!d_result) return HTR_EINVAL;
+   if (!f || !tile) return HTR_EINVAL;
+   if (!g_mix_loaded) return HTR_ENOMIX;
+   cudaStream_t st = (cudaStream_t)stream;
+   cudaError_t e = cudaMemsetAsync(d_result, 0, sizeof(double), st);
+   if (e != cudaSuccess) return cuerr(e);
+   if (rectEmpty(*tile)) return HTR_OK;
+   spectral_radius_kernel<<<blocksFor(*tile, 256), 256, 0, st>>>(*f, *tile, d_result);
+   return cuerr(cudaGetLastError());
+}
+
+int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
+            const htr_rect *bounds, double RK0, double RK1, double deltaTime, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds) return HTR_EINVAL;
+   // Reference task order (src/prometeo.rg:502-578): 0, +chem, +Euler z,y,x, +diffusion z,y,x.
+   cudaStream_t st = (cudaStream_t)stream;
+   {  // Conserved_t = 0 over the tile (RK.InitializeTimeDerivatives, src/prometeo_rk.rg:61-87)
+      zero_rhs_kernel<<<blocksFor(*tile, 128), 128, 0, st>>>(*f, *tile);
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) return cuerr(e);
+   }
+   int rc = HTR_OK;
+   if (chemistry && (rc = htr_add_chemistry_sources(f, tile, stream)) != HTR_OK) return rc;
+   for (int d = 2; d >= 0; d--)
+      if ((rc = htr_euler_flux(scheme, d, f, tile, bounds, RK0, RK1, deltaTime, stream)) != HTR_OK) return rc;
+   if (diffusion)
+      for (int d = 2; d >= 0; d--)
+         if ((rc = htr_diffusion_flux(d, f, tile, bounds, stream)) != HTR_OK) return rc;
+   return rc;
+}
+
+} // extern "C"

@@ -1,0 +1,372 @@
+// Mixture thermodynamics, transport and kinetics evaluated in registers from the parameter
+// block in __constant__ memory.  Free functions over plain arrays; one set per mixture family.
+//
+// Algorithms follow the reference's `Mix` methods, operation order kept so results agree to
+// round-off:  ConstPropMix  src/Mixtures/ConstPropMix.inl:83-167
+//             multi-comp.   src/Mixtures/MultiComponent.inl:59-435, Species.inl:33-357,
+//                           Reaction.inl:34-212
+#pragma once
+#include "htr_mix_layout.h"
+
+namespace htr {
+
+__constant__ MixData c_mix;
+
+#define HTR_DEV __device__ __forceinline__
+#define HTR_UNROLL _Pragma("unroll")
+
+#if !HTR_MULTICOMP
+// ------------------------------------------------------------------------------------------
+// Calorically perfect gas, one species
+// ------------------------------------------------------------------------------------------
+namespace mix {
+HTR_DEV void   ClipYi(double *Yi) {}
+HTR_DEV double GetMolarWeightFromYi(const double *Yi) { return RGAS/c_mix.R; }
+HTR_DEV double GetMolarWeightFromXi(const double *Xi) { return RGAS/c_mix.R; }
+HTR_DEV void   GetMolarFractions(double *Xi, double MixW, const double *Yi) { Xi[0] = Yi[0]; }
+HTR_DEV void   GetMassFractions(double *Yi, double MixW, const double *Xi) { Yi[0] = Xi[0]; }
+HTR_DEV double GetRhoFromRhoYi(const double *rhoYi) { return rhoYi[0]; }
+HTR_DEV void   GetYi(double *Yi, double rho, const double *rhoYi) { Yi[0] = rhoYi[0]/rho; }
+HTR_DEV double GetRho(double P, double T, double MixW) { return P/(c_mix.R*T); }
+HTR_DEV double GetHeatCapacity(double T, const double *Yi) { return c_mix.gamma/(c_mix.gamma - 1)*c_mix.R; }
+HTR_DEV double GetSpeciesEnthalpy(int i, double T) { return c_mix.gamma/(c_mix.gamma - 1)*c_mix.R*T; }
+HTR_DEV double GetSpeciesMolarWeight(int i) { return RGAS/c_mix.R; }
+HTR_DEV double GetInternalEnergy(double T, const double *Yi) { return T*c_mix.R/(c_mix.gamma - 1.0); }
+HTR_DEV double GetTFromInternalEnergy(double e0, double T, const double *Yi) { return e0*(c_mix.gamma - 1.0)/c_mix.R; }
+HTR_DEV double GetTFromRhoAndP(double rho, double MixW, double P) { return P*MixW/(rho*RGAS); }
+HTR_DEV double GetPFromRhoAndT(double rho, double MixW, double T) { return rho*RGAS*T/MixW; }
+HTR_DEV double GetViscosity(double T, const double *Xi) {
+   if (c_mix.viscosityModel == 0) return c_mix.constantVisc;
+   if (c_mix.viscosityModel == 1) return c_mix.powerlawViscRef*pow(T/c_mix.powerlawTempRef, 0.7);
+   return (c_mix.sutherlandViscRef*pow(T/c_mix.sutherlandTempRef, 1.5))*
+          ((c_mix.sutherlandTempRef + c_mix.sutherlandSRef)/(T + c_mix.sutherlandSRef));
+}
+HTR_DEV double GetHeatConductivity(double T, const double *Xi) {
+   const double cp = c_mix.gamma/(c_mix.gamma - 1)*c_mix.R;
+   return cp/c_mix.Prandtl*GetViscosity(T, Xi);
+}
+HTR_DEV double GetGamma(double T, double MixW, const double *Yi) { return c_mix.gamma; }
+HTR_DEV double GetSpeedOfSound(double T, double gamma, double MixW) { return sqrt(gamma*c_mix.R*T); }
+HTR_DEV void   GetDiffusivity(double *Di, double P, double T, double MixW, const double *Xi) { Di[0] = 0.0; }
+HTR_DEV void   GetProductionRates(double *w, double rho, double P, double T, const double *Yi) { w[0] = 0.0; }
+HTR_DEV double Getdpde(double rho, double gamma) { return rho*(gamma - 1); }
+HTR_DEV void   Getdpdrhoi(double *dpdrhoi, double gamma, double T, const double *Yi) { dpdrhoi[0] = c_mix.R*T; }
+} // namespace mix
+
+#else
+// ------------------------------------------------------------------------------------------
+// Multi-component ideal-gas mixture with NASA-9 thermodynamics
+// ------------------------------------------------------------------------------------------
+namespace spec {
+// polynomial range for temperature T (dimensional); switch temperatures are floats promoted to double
+HTR_DEV const double *range(const SpeciesData &s, double T) {
+   return (T > s.cp.TSwitch2) ? s.cp.cpH : ((T > s.cp.TSwitch1) ? s.cp.cpM : s.cp.cpL);
+}
+HTR_DEV double GetCp(const SpeciesData &s, double T) {
+   const double rOvW = RGAS/s.W;
+   const double Tinv = 1.0/T;
+   const double *c = range(s, T);
+   return rOvW*(c[0]*Tinv*Tinv + c[1]*Tinv + c[2] + T*(c[3] + T*(c[4] + T*(c[5] + T*c[6]))));
+}
+HTR_DEV double GetEnthalpy(const SpeciesData &s, double T) {
+   const double rOvW = RGAS/s.W;
+   const double Tinv = 1.0/T;
+   const double *c = range(s, T);
+   const double E = -c[0]*Tinv + c[1]*log(T) + c[7] + T*(c[2] + T*(c[3]*0.50 + T*(c[4]/3 + T*(c[5]*0.25 + c[6]/5*T))));
+   return E*rOvW;
+}
+HTR_DEV double GetFreeEnthalpy(const SpeciesData &s, double T) {   // H/(RT) - S/R
+   const double Tinv = 1.0/T;
+   const double logT = log(T);
+   const double *c = range(s, T);
+   const double G = -0.5*c[0]*Tinv*Tinv + c[1]*Tinv*(1.0 + logT) + c[2]*(1.0 - logT) + c[7]*Tinv - c[8];
+   return G - 0.5*T*(c[3] + T*(c[4]/3 + T*(c[5]/6 + 0.1*T*c[6])));
+}
+// reduced collision integrals, rational fits in T* = T kb/eps
+HTR_DEV double omega_mu(double T) {
+   const double num = 3.3530622607 + T*(2.53272006 + T*(2.9024238575 + T*0.11186138893));
+   const double den = 0.8662326188 + T*(1.3913958626 + T*(3.158490576 + T*(0.18973411754 + T*0.00018682962894)));
+   return num/den;
+}
+HTR_DEV double omega_D(double T) {
+   const double num = 6.8728271691 + T*(9.4122316321 + T*(7.7442359037 + T*0.23424661229));
+   const double den = 1.45337701568 + T*(5.2269794238 + T*(9.7108519575 + T*(0.46539437353 + T*0.00041908394781)));
+   return num/den;
+}
+HTR_DEV double GetMu(const SpeciesData &s, double T) {
+   const double num = 5*sqrt(PI*s.W/Na*kb*T);
+   const double den = 16*PI*pow(s.diff.sigma, 2)*omega_mu(T*s.diff.kbOveps);
+   return num/den;
+}
+// Stockmayer-corrected binary diffusion coefficient of the pair (a, b)
+HTR_DEV double GetDif(const SpeciesData &a, const SpeciesData &b, double P, double T) {
+   double xi = 1.0;
+   if ((a.diff.mu*b.diff.mu == 0.0) && (a.diff.mu + b.diff.mu != 0.0)) {
+      double mup, alp, epr;     // polar / non-polar pair
+      if (a.diff.mu != 0.0) {
+         mup = a.diff.mu/sqrt(4*PI*eps_0*kb*pow(a.diff.sigma, 3)/a.diff.kbOveps);
+         alp = b.diff.alpha/pow(b.diff.sigma, 3);
+         epr = sqrt(b.diff.kbOveps/a.diff.kbOveps);
+      } else {
+         mup = b.diff.mu/sqrt(4*PI*eps_0*kb*pow(b.diff.sigma, 3)/b.diff.kbOveps);
+         alp = a.diff.alpha/pow(a.diff.sigma, 3);
+         epr = sqrt(a.diff.kbOveps/b.diff.kbOveps);
+      }
+      xi = 1 + 0.25*mup*alp*epr;
+   }
+   const double sigmaij = 0.5*(a.diff.sigma + b.diff.sigma)*pow(xi, -1./6);
+   const double kboEpsij = sqrt(a.diff.kbOveps*b.diff.kbOveps)/(xi*xi);
+   const double omega11 = omega_D(T*kboEpsij);
+   const double invWij = (a.W + b.W)/(a.W*b.W);
+   const double num = 3*sqrt(2*PI*pow(kb, 3)*pow(T, 3)*Na*invWij);
+   const double den = 16*PI*P*sigmaij*sigmaij*omega11;
+   return num/den;
+}
+HTR_DEV double GetSelfDiffusion(const SpeciesData &s, double T) {
+   const double num = 3*sqrt(PI*kb*T*s.W/Na);
+   const double den = 8*PI*pow(s.diff.sigma, 2)*omega_D(T*s.diff.kbOveps);
+   return num/den;
+}
+HTR_DEV double GetFZrot(const SpeciesData &s, double T) {
+   const double tmp = 1.0/(s.diff.kbOveps*T);
+   return 1 + 0.5*pow(PI, 1.5)*sqrt(tmp) + (2 + 0.25*PI*PI)*tmp + pow(PI, 1.5)*pow(tmp, 1.5);
+}
+// Species conductivity: monatomic (Eucken 15/4) or modified-Eucken with rotational relaxation
+HTR_DEV double GetLam(const SpeciesData &s, double T) {
+   const double mu = GetMu(s, T);
+   if (s.diff.Geom == 0) return 15.0/4*mu*RGAS/s.W;
+   const bool lin = (s.diff.Geom == 1);
+   const double CvROvR = lin ? 1.0 : 1.5;
+   const double CvT = 1.5*RGAS;
+   const double CvR = CvROvR*RGAS;
+   const double CvV = GetCp(s, T)*s.W - (lin ? 3.5 : 4.0)*RGAS;
+   const double Dkk = GetSelfDiffusion(s, T);
+   const double fV = Dkk/mu;
+   const double Zrot = s.diff.Z298*GetFZrot(s, 298.0)/GetFZrot(s, T);
+   const double A = 2.5 - fV;
+   const double B = Zrot + 2/PI*(5./3*CvROvR + fV);
+   const double fT = 2.5*(1. - 2*CvR*A/(PI*CvT*B));
+   const double fR = fV*(1. + 2*A/(PI*B));
+   return mu/s.W*(fT*CvT + fR*CvR + fV*CvV);
+}
+} // namespace spec
+
+namespace mix {
+HTR_DEV void ClipYi(double *Yi) {
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) { Yi[i] = fmax(Yi[i], 1e-60); Yi[i] = fmin(Yi[i], 1.0); }
+}
+HTR_DEV double GetMolarWeightFromYi(const double *Yi) {
+   double s = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) s += Yi[i]/c_mix.species[i].W;
+   return 1.0/s;
+}
+HTR_DEV double GetMolarWeightFromXi(const double *Xi) {
+   double s = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) s += Xi[i]*c_mix.species[i].W;
+   return s;
+}
+HTR_DEV void GetMolarFractions(double *Xi, double MixW, const double *Yi) {
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Xi[i] = Yi[i]*MixW/c_mix.species[i].W;
+}
+HTR_DEV void GetMassFractions(double *Yi, double MixW, const double *Xi) {
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Yi[i] = Xi[i]*c_mix.species[i].W/MixW;
+}
+HTR_DEV double GetRhoFromRhoYi(const double *rhoYi) {
+   double rho = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) rho += rhoYi[i];
+   return rho;
+}
+HTR_DEV void GetYi(double *Yi, double rho, const double *rhoYi) {
+   const double irho = 1.0/rho;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Yi[i] = irho*rhoYi[i];
+}
+HTR_DEV double GetRho(double P, double T, double MixW) { return P*MixW*c_mix.iMixWRef/T; }
+HTR_DEV double GetHeatCapacity(double Tn, const double *Yi) {
+   const double T = Tn*c_mix.TRef;
+   double cp = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) cp += Yi[i]*spec::GetCp(c_mix.species[i], T);
+   return cp*c_mix.iCpRef;
+}
+HTR_DEV double GetSpeciesEnthalpy(int i, double T) { return spec::GetEnthalpy(c_mix.species[i], T*c_mix.TRef)*c_mix.ieRef; }
+HTR_DEV double GetSpeciesMolarWeight(int i) { return c_mix.species[i].W; }
+HTR_DEV double GetInternalEnergy(double Tn, const double *Yi) {
+   const double T = Tn*c_mix.TRef;
+   double e = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) e += Yi[i]*(spec::GetEnthalpy(c_mix.species[i], T) - RGAS*T/c_mix.species[i].W);
+   return e*c_mix.ieRef;
+}
+// Newton iteration on e(T) = e0 from the caller's guess (step tolerance 1e-8 on non-dimensional T)
+HTR_DEV double GetTFromInternalEnergy(double e0, double T, const double *Yi) {
+   double dfdT = 1.0;
+   for (int j = 0; j < 1000; j++) {
+      const double f = e0 - GetInternalEnergy(T, Yi);
+      if (fabs(f/dfdT) < 1e-8) break;
+      dfdT = 0.0;
+      HTR_UNROLL
+      for (int i = 0; i < nSpec; i++)
+         dfdT += Yi[i]*(spec::GetCp(c_mix.species[i], T*c_mix.TRef) - RGAS/c_mix.species[i].W)*c_mix.iCpRef;
+      T += f/dfdT;
+   }
+   return T;
+}
+HTR_DEV double GetTFromRhoAndP(double rho, double MixW, double P) { return P*MixW*c_mix.iMixWRef/rho; }
+HTR_DEV double GetPFromRhoAndT(double rho, double MixW, double T) { return rho*T/(MixW*c_mix.iMixWRef); }
+// Wilke mixing rule
+HTR_DEV double GetViscosity(double Tn, const double *Xi) {
+   const double T = Tn*c_mix.TRef;
+   double muk[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) muk[i] = spec::GetMu(c_mix.species[i], T);
+   double mu = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      double den = 0.0;
+      HTR_UNROLL
+      for (int j = 0; j < nSpec; j++) {
+         double Phi = 1 + sqrt(muk[i]/muk[j])*pow(c_mix.species[j].W/c_mix.species[i].W, 0.25);
+         Phi *= Phi/sqrt(8*(1 + c_mix.species[i].W/c_mix.species[j].W));
+         den += Xi[j]*Phi;
+      }
+      mu += Xi[i]*muk[i]/den;
+   }
+   return mu*c_mix.imuRef;
+}
+HTR_DEV double GetHeatConductivity(double Tn, const double *Xi) {
+   const double T = Tn*c_mix.TRef;
+   double a = 0.0, b = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      const double lami = spec::GetLam(c_mix.species[i], T);
+      a += Xi[i]*lami;
+      b += Xi[i]/lami;
+   }
+   return 0.5*(a + 1.0/b)*c_mix.ilamRef;
+}
+HTR_DEV double GetGamma(double T, double MixW, const double *Yi) {
+   const double cp = GetHeatCapacity(T, Yi);
+   const double Wr = MixW*c_mix.iMixWRef;
+   return cp/(cp - 1.0/Wr);
+}
+HTR_DEV double GetSpeedOfSound(double T, double gamma, double MixW) { return sqrt(gamma*T/(MixW*c_mix.iMixWRef)); }
+HTR_DEV void GetDiffusivity(double *Di, double Pn, double Tn, double MixW, const double *Xi) {
+   const double T = Tn*c_mix.TRef;
+   const double P = Pn*c_mix.PRef;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Di[i] = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      HTR_UNROLL
+      for (int j = 0; j < i; j++) {
+         const double invDij = 1.0/spec::GetDif(c_mix.species[i], c_mix.species[j], P, T);
+         Di[i] += Xi[j]*invDij;
+         Di[j] += Xi[i]*invDij;
+      }
+   }
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      double num = 0.0;
+      HTR_UNROLL
+      for (int j = 0; j < nSpec; j++)
+         if (j != i) num += Xi[j]*c_mix.species[j].W;
+      Di[i] = num/(MixW*Di[i])*c_mix.iDiRef;
+   }
+}
+HTR_DEV double Getdpde(double rho, double gamma) { return rho*(gamma - 1); }
+HTR_DEV void Getdpdrhoi(double *dpdrhoi, double gamma, double Tn, const double *Yi) {
+   const double T = Tn*c_mix.TRef;
+   double e = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      dpdrhoi[i] = spec::GetEnthalpy(c_mix.species[i], T) - RGAS*T/c_mix.species[i].W;
+      e += Yi[i]*dpdrhoi[i];
+   }
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++)
+      dpdrhoi[i] = (RGAS*T/c_mix.species[i].W + (gamma - 1)*(e - dpdrhoi[i]))*c_mix.ieRef;
+}
+
+// ---- finite-rate kinetics ----
+HTR_DEV double rateCoeff(const Arrhenius &k, double T) {
+   double Kf = k.A;
+   if (k.n != 0.0) Kf *= pow(T, (double)k.n);
+   if (fabs(k.EovR) > 1e-5) Kf *= exp(-k.EovR/T);
+   return Kf;
+}
+HTR_DEV double massAction(const StoichTerm *t, int n, const double *C) {
+   double a = 1.0;
+   for (int i = 0; i < n; i++) {
+      const int ind = t[i].ind;
+      if (t[i].nu == 1) a *= C[ind];
+      else              a *= pow(C[ind], (double)t[i].nu);
+   }
+   return a;
+}
+template<class R>
+HTR_DEV double backwardRateCoeff(const R &r, double Kf, double P, double T, const double *G) {
+   double sumNu = 0.0, sumNuG = 0.0;
+   for (int i = 0; i < r.Neducts; i++) { sumNu -= r.educts[i].nu; sumNuG -= r.educts[i].nu*G[r.educts[i].ind]; }
+   for (int i = 0; i < r.Npducts; i++) { sumNu += r.pducts[i].nu; sumNuG += r.pducts[i].nu*G[r.pducts[i].ind]; }
+   const double lnKc = -sumNuG - sumNu*(log(T) + log(RGAS/P));
+   return Kf*exp(-lnKc);
+}
+template<class R>
+HTR_DEV double netRate(const R &r, double P, double T, const double *C, const double *G) {
+   const double Kf = rateCoeff(r.k, T);
+   const double a = massAction(r.educts, r.Neducts, C);
+   double Kb = 0.0, b = 1.0;
+   if (r.has_backward) {
+      Kb = backwardRateCoeff(r, Kf, P, T, G);
+      b = massAction(r.pducts, r.Npducts, C);
+   }
+   return Kf*a - Kb*b;
+}
+template<class R>
+HTR_DEV void scatter(const R &r, double rate, double *w) {
+   for (int i = 0; i < r.Neducts; i++) w[r.educts[i].ind] -= r.educts[i].nu*rate;
+   for (int i = 0; i < r.Npducts; i++) w[r.pducts[i].ind] += r.pducts[i].nu*rate;
+}
+// w_i in computational units from non-dimensional rho, P, T and mass fractions
+HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, const double *Yi) {
+   const double T = Tn*c_mix.TRef;
+   const double P = Pn*c_mix.PRef;
+   const double rho = rhon*c_mix.rhoRef;
+   double G[nSpec], C[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      w[i] = 0.0;
+      C[i] = Yi[i]*rho/c_mix.species[i].W;
+      G[i] = spec::GetFreeEnthalpy(c_mix.species[i], T);
+   }
+#if HTR_NREAC > 0
+   HTR_UNROLL
+   for (int r = 0; r < HTR_NREAC; r++)
+      scatter(c_mix.reactions[r], netRate(c_mix.reactions[r], P, T, C, G), w);
+#endif
+#if HTR_NTBREAC > 0
+   HTR_UNROLL
+   for (int r = 0; r < HTR_NTBREAC; r++) {
+      const CollisionReaction &R = c_mix.tbReactions[r];
+      double c = 1.0;
+      if (R.Nthirdb > 0) {
+         c = P/(RGAS*T);
+         for (int i = 0; i < R.Nthirdb; i++) c += C[R.thirdb[i].ind]*(R.thirdb[i].nu - 1.0);
+      }
+      scatter(R, c*netRate(R, P, T, C, G), w);
+   }
+#endif
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) w[i] *= c_mix.species[i].W*c_mix.iwiRef;
+}
+} // namespace mix
+#endif // HTR_MULTICOMP
+
+} // namespace htr

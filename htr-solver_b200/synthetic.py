@@ -1,0 +1,75 @@
+"""Deterministic synthetic inputs for the RHS hot path (numpy, host side).
+
+Taylor-Green 3-D vortex primitives as the reference initialises them
+(src/prometeo_init.rg:134-158), on a tri-periodic box with cell centres (i+1/2) L/N, uniform or
+smoothly stretched metrics, all-standard node types (periodic directions,
+src/prometeo_metric.rg:142-148).  Only primitives are produced here; density, transport
+properties and the conserved vector come from the UpdatePropertiesFromPrimitive /
+UpdateConservedFromPrimitive kernels (or, in the tests, from the oracle).
+"""
+import numpy as np
+
+# reference input files these parameter sets come from
+CONSTPROP_3DPERIODIC = {"type": "ConstPropMix", "gasConstant": 1.0, "gamma": 1.4, "prandtl": 0.71,
+                        "viscosityModel": {"type": "Constant", "Visc": 0.0}}          # solverTests/3DPeriodic_TENO/base.json
+CONSTPROP_VISCOUS = {"type": "ConstPropMix", "gasConstant": 1.0, "gamma": 1.4, "prandtl": 0.71,
+                     "viscosityModel": {"type": "Constant", "Visc": 5.0e-3}}
+AIRMIX_3DPERIODIC = {"type": "AirMix", "LRef": 1.0, "TRef": 500.0, "PRef": 100000.0,
+                     "XiRef": {"Species": [{"Name": "N2", "MolarFrac": 0.79}, {"Name": "O2", "MolarFrac": 0.21}]}}  # solverTests/3DPeriodic_Air/base.json
+AIR_SPECIES = ["N2", "O2", "NO", "N", "O"]
+
+
+def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=0.0, species_wave=0.0,
+                 front=0.0, dtype=np.float64):
+    """Host fields of an (nx,ny,nz)=n periodic box.  Returns dict name -> array [z][y][x](comp).
+
+    stretch > 0      multiplies the metrics by 1 + stretch*sin(coordinate): a smooth non-uniform grid
+    species_wave > 0 (multi-component only) adds smooth O2/NO/N/O mole-fraction waves
+    front > 0        superposes a tanh temperature/pressure front of that relative strength in x
+                     (steep gradients: exercises the nonlinear TENO weights and the shock sensor)
+    """
+    nx, ny, nz = (n, n, n) if np.isscalar(n) else n
+    multi = mix_cfg["type"] != "ConstPropMix"
+    nspec = 5 if multi else 1
+    if p0 is None:
+        p0, T0, U = (1.0, 1.0, 0.002634364032587426) if multi else (100.0, 100.0, 1.0)
+    x = (np.arange(nx) + 0.5) * width / nx
+    y = (np.arange(ny) + 0.5) * width / ny
+    z = (np.arange(nz) + 0.5) * width / nz
+    Z, Y, X = np.meshgrid(z, y, x, indexing="ij")
+    f = {}
+    for d, (nn, c) in enumerate(((nx, X), (ny, Y), (nz, Z))):
+        m = (nn / width) * (1.0 + stretch * np.sin(c + 0.3 * d))
+        for kind in "eds":
+            f[("dcsi_", "deta_", "dzet_")[d] + kind] = np.ascontiguousarray(m * (1.0 + 0.01 * stretch * "eds".index(kind)))
+        f[("nType_x", "nType_y", "nType_z")[d]] = np.zeros((nz, ny, nx), dtype=np.int32)
+    R = mix_cfg.get("gasConstant", 1.0)
+    rho0 = p0 / (R * T0)
+    vel = np.zeros((nz, ny, nx, 3))
+    vel[..., 0] = U * np.sin(X) * np.cos(Y) * np.cos(Z)
+    vel[..., 1] = -U * np.cos(X) * np.sin(Y) * np.cos(Z)
+    P = p0 + rho0 * U ** 2 / 16.0 * (np.cos(2 * Z) + 2.0) * (np.cos(2 * X) + np.cos(2 * Y))
+    T = P / (rho0 * R)
+    if front > 0.0:
+        s = np.tanh((X - 0.5 * width) * 8.0 / width * nx / 32.0) * np.cos(Y) * np.cos(Z)
+        T = T * (1.0 + front * s)
+        P = P * (1.0 + 0.5 * front * s)
+    Xi = np.zeros((nz, ny, nx, nspec))
+    if multi:
+        ref = {s["Name"]: s["MolarFrac"] for s in mix_cfg["XiRef"]["Species"]}
+        for i, s in enumerate(AIR_SPECIES):
+            Xi[..., i] = ref.get(s, 1.0e-60)
+        if species_wave > 0.0:
+            w = species_wave
+            Xi[..., 1] += w * 0.05 * np.sin(X) * np.cos(2 * Y)
+            Xi[..., 2] = w * 0.01 * (1.1 + np.sin(2 * X + Z))
+            Xi[..., 3] = w * 0.002 * (1.1 + np.cos(Y + 2 * Z))
+            Xi[..., 4] = w * 0.005 * (1.1 + np.sin(X + Y + Z))
+            Xi[..., 0] = 1.0 - Xi[..., 1:].sum(axis=-1)
+    else:
+        Xi[..., 0] = 1.0
+    f["pressure"] = np.ascontiguousarray(P, dtype=dtype)
+    f["temperature"] = np.ascontiguousarray(T, dtype=dtype)
+    f["velocity"] = vel
+    f["MolarFracs"] = Xi
+    return f

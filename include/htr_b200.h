@@ -1,0 +1,118 @@
+/* htr_b200.h -- C ABI of the B200-native HTR right-hand-side engine.
+ *
+ * One shared library per mixture (libhtr_b200_<Mix>.so), like the reference builds one
+ * executable per -DEOS=<Mix> (src/prometeo_const.h:37-41, src/Makefile:68-70).
+ * Every entry point is the Legion-free body of one reference leaf task: it takes what the
+ * task's gpu_base_impl extracts from its PhysicalRegions -- one affine accessor
+ * (base pointer + byte strides, Realm::AffineAccessor semantics) per field, the
+ * execution rectangle (index space of the written region) and args.Fluid_bounds --
+ * and launches hand-written sm_100a kernels on the caller's stream.  All pointers in
+ * htr_fluid are DEVICE pointers.  No torch types, no Legion types.
+ *
+ * The Legion side (register_{rhs,sensor,chem,variables,cfl}_tasks, src/prometeo_*.h:39)
+ * is htr-solver_b200/csrc/legion_adapter.cc, which only unpacks regions into these calls
+ * (INTEGRATION.md).
+ *
+ * Return value: 0 on success, a negative HTR_E* code on a usage error; CUDA launch
+ * failures are returned as 1000+cudaError_t.  The reference aborts (assert) on the
+ * same conditions (src/prometeo_rhs.cc:43-44).
+ */
+#ifndef HTR_B200_H
+#define HTR_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HTR_OK 0
+#define HTR_EINVAL (-1)   /* bad argument (direction, scheme, empty accessor that the task reads) */
+#define HTR_ENOMIX (-2)   /* mixture not loaded: call htr_set_mixture first (LoadMixtureTask, src/prometeo_mixture.cu:35-47) */
+#define HTR_EMIXTYPE (-3) /* constructor for another mixture than the one this library was built for */
+
+/* Affine accessor: address(p) = base + p.x*stride[0] + p.y*stride[1] + p.z*stride[2], p in GLOBAL
+ * grid coordinates, strides in BYTES (replaces FieldAccessor<...,Realm::AffineAccessor<T,3,coord_t>>,
+ * src/Utils/task_helper.hpp:99-102).  Vector fields are MyArray<double,n>: n contiguous doubles
+ * per cell (src/prometeo_types.h:321-323). */
+typedef struct { void *base; int64_t stride[3]; } htr_acc;
+
+/* Inclusive rectangle, Legion Rect<3> semantics. */
+typedef struct { int64_t lo[3]; int64_t hi[3]; } htr_rect;
+
+/* The Fluid_columns fields the hot path touches (src/prometeo_types.h:49-113), same names. */
+typedef struct {
+   htr_acc nType_x, nType_y, nType_z;            /* int32 */
+   htr_acc dcsi_e, deta_e, dzet_e;               /* double */
+   htr_acc dcsi_d, deta_d, dzet_d;
+   htr_acc dcsi_s, deta_s, dzet_s;
+   htr_acc rho, mu, lam, Di, SoS;                /* Di: nSpec doubles */
+   htr_acc pressure, temperature, MassFracs, MolarFracs, velocity;
+   htr_acc Conserved, Conserved_old, Conserved_t, Conserved_t_old;   /* nEq doubles */
+   htr_acc shockSensorX, shockSensorY, shockSensorZ;                 /* C++ bool, 1 byte */
+   htr_acc DucrosSensor;
+} htr_fluid;
+
+/* Euler schemes = the reference's task families (src/prometeo_types.h:184-283 TID_UpdateUsing*EulerFlux*). */
+enum { HTR_SCHEME_HYBRID = 0, HTR_SCHEME_TENO = 1, HTR_SCHEME_TENOA = 2,
+       HTR_SCHEME_TENOLAD = 3, HTR_SCHEME_SKEWSYMMETRIC = 4 };
+enum { HTR_XDIR = 0, HTR_YDIR = 1, HTR_ZDIR = 2 };
+
+/* ---- library identity ---- */
+int  htr_nspec(void);
+int  htr_neq(void);
+const char *htr_mixture_name(void);
+int  htr_sizeof_mix(void);        /* == sizeof(reference struct Mix) for this mixture */
+const char *htr_build_info(void); /* arch, flags */
+
+/* ---- mixture (replaces Mix::Mix(const Config&) + LoadMixtureTask) ----
+ * The constructors fill `mix_out` (htr_sizeof_mix() bytes) with a POD that is byte-identical
+ * to the reference's struct Mix, so an adapter may instead pass args.mix straight to
+ * htr_set_mixture.  ConstPropMix: src/Mixtures/ConstPropMix.inl:31-52 (visc_model 0 Constant{p0=Visc},
+ * 1 PowerLaw{p0=ViscRef,p1=TempRef}, 2 Sutherland{p0=ViscRef,p1=TempRef,p2=SRef}).
+ * Multi-component: src/Mixtures/AirMix.hpp:319-332 + MultiComponent.inl:438-488; names = n x 10 chars. */
+int htr_mix_init_constprop(void *mix_out, double gasConstant, double gamma, double prandtl,
+                           int visc_model, double p0, double p1, double p2);
+int htr_mix_init_multicomp(void *mix_out, double LRef, double PRef, double TRef,
+                           int n, const char *names, const double *molarFracs);
+int htr_set_mixture(const void *mix, size_t bytes);   /* copies into __constant__ memory of the current device */
+
+/* ---- leaf tasks (device pointers; asynchronous on `stream`, a cudaStream_t) ----
+ * tile   = index space of the region the task writes (src/prometeo_rhs.cc:70-71)
+ * bounds = args.Fluid_bounds, the global box stencil points wrap on
+ *          (src/Utils/PointDomain_helper.hpp:156-182) */
+/* UpdateUsing{Hybrid,TENO,TENOA,TENOLAD,SkewSymmetric}EulerFlux{X,Y,Z}Task (src/prometeo_rhs.cc:37-376) */
+int htr_euler_flux(int scheme, int dir, const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds,
+                   double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+/* UpdateUsingDiffusionFlux{X,Y,Z}Task (src/prometeo_rhs.cc:410-467) */
+int htr_diffusion_flux(int dir, const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds, void *stream);
+/* UpdateDucrosSensorTask (src/prometeo_sensor.cc:37-79) */
+int htr_ducros_sensor(const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds,
+                      double vorticityScale, void *stream);
+/* UpdateShockSensorTask<dir> (src/prometeo_sensor.cc:83-138) */
+int htr_shock_sensor(int dir, const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds, void *stream);
+/* AddChemistrySourcesTask (src/prometeo_chem.cc:78-112) */
+int htr_add_chemistry_sources(const htr_fluid *f, const htr_rect *tile, void *stream);
+/* UpdateChemistryTask (src/prometeo_chem.cc:36-71) */
+int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double Integrator_deltaTime, void *stream);
+/* Cells whose implicit integration hit the step/iteration caps since the last call (the reference
+ * asserts there, src/Utils/math_utils.hpp:233,240).  Synchronises the device and resets the counter. */
+int htr_chemistry_failures(void);
+/* UpdatePrimitiveFromConservedTask / UpdatePropertiesFromPrimitiveTask / UpdateConservedFromPrimitiveTask
+ * (src/prometeo_variables.cc:138-173, :36-86, :92-132) */
+int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream);
+int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream);
+int htr_update_conserved_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream);
+/* CalculateMaxSpectralRadiusTask (src/prometeo_cfl.cc:36-93): the tile maximum is written to
+ * *d_result (device double, the DeferredValue of the GPU variant, src/prometeo_cfl.hpp:181-189). */
+int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_result, void *stream);
+
+/* ---- fused stage (B200 fast path; same arithmetic, one pass per direction group) ----
+ * One UpdateDerivatives pass (src/prometeo.rg:502-578): Conserved_t = 0 (+ chemistry source)
+ * + Euler z,y,x + diffusion z,y,x, in the reference's accumulation order. */
+int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
+            const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -61,6 +61,8 @@ int htr_oracle_init_multicomp(double LRef, double PRef, double TRef,
  *  [11]T(e) [16..]Xi(Yi) [16+n..]Di [16+2n..]w_i [16+3n..]dpdrhoi ; inputs are
  *  non-dimensional P,T and mass fractions. */
 void htr_oracle_mix_eval(double P, double T, const double *Yi, double *out);
+int htr_oracle_mix_bytes(void *out);       /* copies sizeof(Mix) bytes, returns the size */
+int htr_oracle_mix_table_bytes(void);      /* offset of Mix::PRef (0 for ConstPropMix) */
 double htr_oracle_species_enthalpy(int i, double T);
 double htr_oracle_species_W(int i);
 

@@ -323,6 +323,16 @@ void htr_oracle_mix_eval(double P, double T, const double *Yi_, double *out) {
       out[16 + 2*nSpec + i] = w[i]; out[16 + 3*nSpec + i] = dp[i];
    }
 }
+// Raw bytes of the reference's `struct Mix` (the POD the reference ships in every task's Args,
+// src/prometeo_rhs.hpp:183) and the size of its leading constant species/reaction tables.
+int htr_oracle_mix_bytes(void *out) { memcpy(out, &mix(), sizeof(Mix)); return (int)sizeof(Mix); }
+int htr_oracle_mix_table_bytes(void) {
+#ifdef HTR_EOS_IS_CONSTPROP
+   return 0;
+#else
+   return (int)((const char*)&mix().PRef - (const char*)&mix());
+#endif
+}
 double htr_oracle_species_enthalpy(int i, double T) { return mix().GetSpeciesEnthalpy(i, T); }
 double htr_oracle_species_W(int i) { return mix().GetSpeciesMolarWeight(i); }
 
