@@ -1,0 +1,398 @@
+#!/usr/bin/env python3
+"""bench.py -- fp64 RHS cell-updates/s of the HTR hot path on B200 (contract: see DESIGN.md, section Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl reference]
+
+A "step" is one UpdateDerivatives pass (src/prometeo.rg:502-578) over the rank's block:
+Conserved_t = 0 (+ chemistry source) + Euler z,y,x + diffusion z,y,x.  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+
+import numpy as np  # noqa: E402
+
+# name -> (mixture config key, n per GPU, scheme, diffusion, chemistry, reference file it is scaled from)
+WORKLOADS = {
+    "air512":        ("AIRMIX_3DPERIODIC", 512, "Hybrid", True, True,  "solverTests/3DPeriodic_Air/base.json scaled to 512^3 per GPU (north-star target)"),
+    "air256":        ("AIRMIX_3DPERIODIC", 256, "Hybrid", True, True,  "solverTests/3DPeriodic_Air/base.json scaled to 256^3"),
+    "tg128_hybrid":  ("CONSTPROP_3DPERIODIC", 128, "Hybrid", True, False, "solverTests/3DPeriodic/base.json scaled to 128^3"),
+    "tg128_teno":    ("CONSTPROP_3DPERIODIC", 128, "TENO", True, False, "solverTests/3DPeriodic_TENO/base.json scaled to 128^3"),
+    "tg512_skew":    ("CONSTPROP_VISCOUS", 512, "SkewSymmetric", True, False, "solverTests/3DPeriodic_SkewSymmetric/base.json scaled to 512^3, Visc=5e-3"),
+}
+DEFAULT_WORKLOAD = "air512"
+
+
+def algorithmic_bytes(nspec, scheme, diffusion, chemistry):
+    """Compulsory HBM bytes per RHS cell-update: every needed field read once,
+    Conserved_t written once.  B = 8*(nEq*(2+[N>1]) + 3N + 18) + 15 with diffusion and all inputs."""
+    neq = nspec + 4
+    if diffusion:
+        return 8 * (neq * (2 + (1 if nspec > 1 else 0)) + 3 * nspec + 18) + 15
+    return 8 * (neq * (2 + (1 if nspec > 1 else 0)) + nspec + 6 + 3) + 15
+
+
+def kernel_bytes(kind, nspec, scheme):
+    """Algorithmic bytes per cell of ONE launch of a per-direction kernel (fields it must read once +
+    Conserved_t read-modify-write), used for the dominant-kernel roofline."""
+    neq = nspec + 4
+    if kind == "euler":
+        b = 8 * (neq + 3 + 3 + nspec + 1) + 4 + 2 * 8 * neq      # Conserved, rho/SoS/p, velocity, MassFracs, m_e, nType, Conserved_t RMW
+        if scheme == "Hybrid":
+            b += 1
+        if nspec > 1 and scheme != "SkewSymmetric":
+            b += 8 * neq                                           # Conserved_old (limiter)
+        return b
+    if kind == "diffusion":
+        return 8 * (nspec + 1 + nspec + 3 + nspec + 3 + 4) + 12 + 2 * 8 * neq   # rhoYi, T, Xi, rho/mu/lam, Di, velocity, m_s+3 m_d, 3 nType, RMW
+    if kind == "chem":
+        return 8 * (3 + nspec) + 2 * 8 * nspec
+    if kind == "zero":
+        return 8 * neq
+    raise KeyError(kind)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32):
+    """Synthetic Taylor-Green primitives generated slab by slab on the host, uploaded into the block
+    (interior + halo, which for a periodic global box is just more of the same analytic field), then
+    properties and conserved variables computed by the product kernels over the whole allocation."""
+    import torch
+    from htr_solver_b200 import synthetic
+    nx = ny = nz = n
+    h = halo
+    tot = n + 2 * h
+    for k0 in range(0, tot, slab):
+        k1 = min(tot, k0 + slab)
+        f = synthetic.taylor_green((tot, tot, tot), cfg, zslab=(k0, k1), species_wave=1.0 if cfg["type"] != "ConstPropMix" else 0.0,
+                                   offset=(offset[0] - h, offset[1] - h, offset[2] - h), global_n=global_n)
+        for name, arr in f.items():
+            if name in fl.t:
+                fl.t[name][k0:k1].copy_(torch.from_numpy(np.ascontiguousarray(arr)))
+    from htr_solver_b200 import Rect
+    o = fl.origin
+    full = Rect.make((o[0] - h, o[1] - h, o[2] - h), (o[0] + n - 1 + h, o[1] + n - 1 + h, o[2] + n - 1 + h))
+    solver.UpdatePropertiesFromPrimitive(fl, tile=full)
+    solver.UpdateConservedFromPrimitive(fl, tile=full)
+    fl.t["Conserved_old"].copy_(fl.t["Conserved"])
+    torch.cuda.synchronize()
+
+
+def cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=20.0, n=None):
+    """Times the reference's own CPU tasks (oracle/_ref, `-O3 -fopenmp -DREALM_USE_OPENMP`, all host
+    threads) on a bounded sample of the workload: the same Taylor-Green box at n^3.
+    Returns (cell-updates/s, description dict).  TEST/BASELINE infrastructure only."""
+    from oracle_lib import Oracle, alloc_fields
+    from htr_solver_b200 import synthetic
+    cfg = getattr(synthetic, cfgname)
+    mix = cfg["type"]
+    try:
+        o = Oracle(mix, omp=True, kind="reference")
+        kind = "reference"
+    except FileNotFoundError:
+        o = Oracle(mix, omp=False)
+        kind = o.kind
+    o.init_mix(cfg)
+    if n is None:
+        n = 160 if mix != "ConstPropMix" else 192
+    f = alloc_fields(n, n, n, o.nspec)
+    prim = synthetic.taylor_green(n, cfg, species_wave=1.0 if mix != "ConstPropMix" else 0.0)
+    for k, v in prim.items():
+        f[k][...] = v
+    o.update_properties_from_primitive(f)
+    o.update_conserved_from_primitive(f)
+    f["Conserved_old"][...] = f["Conserved"]
+    o.ducros_sensor(f, 1.0)
+    for d in range(3):
+        o.shock_sensor(f, d)
+    o.rhs(f, scheme, diffusion, chemistry, 1.0, 0.0, 1e-3)          # warm-up
+    times = []
+    t_end = time.time() + budget_s
+    while len(times) < 2 or (time.time() < t_end and len(times) < 50):
+        t0 = time.perf_counter()
+        o.rhs(f, scheme, diffusion, chemistry, 1.0, 0.0, 1e-3)
+        times.append(time.perf_counter() - t0)
+    best = min(times)
+    return n ** 3 / best, {"kind": kind, "cores": o.threads, "sample": f"{n}^3 box of the same workload, best of {len(times)} RHS evaluations after 1 warm-up",
+                           "host_cpus": os.cpu_count(), "ms_per_rhs": best * 1e3, "n": n}
+
+
+def run_reference(args, rank, world):
+    name = args.workload
+    cfgname, n, scheme, diffusion, chemistry, src = WORKLOADS[name]
+    if rank != 0:
+        return
+    # each "step" = one RHS evaluation of the bounded sample; steps/warmup are honoured on the sample
+    from oracle_lib import Oracle  # noqa: F401
+    val, desc = cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=max(5.0, min(60.0, 4.0 * args.steps)))
+    line = {"impl": "reference", "metric": "fp64 RHS cell-updates/s", "value": val, "unit": "cell-updates/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": desc["ms_per_rhs"],
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": name, "source": src, "scheme": scheme, "diffusion": diffusion, "chemistry": chemistry,
+                       "grid_per_gpu": [n, n, n], "sample_grid": [desc["n"]] * 3},
+            "cpu_baseline": {"value": val, "unit": "cell-updates/s", "cores": desc["cores"], "kind": desc["kind"], "sample": desc["sample"]},
+            "e2e": {"value": val, "unit": "cell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def tiles_for(world):
+    return {1: (1, 1, 1), 2: (1, 1, 2), 4: (1, 2, 2), 8: (2, 2, 2)}.get(world) or (1, 1, world)
+
+
+def run_gpu(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import htr_solver_b200 as htr
+    from htr_solver_b200 import synthetic
+
+    name = args.workload
+    cfgname, n, scheme, diffusion, chemistry, src = WORKLOADS[name]
+    if args.n:
+        n = args.n
+    cfg = getattr(synthetic, cfgname)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    solver = htr.Solver(cfg)
+    nspec, neq = solver.nspec, solver.neq
+    tiles = tiles_for(world)
+    gN = (n * tiles[0], n * tiles[1], n * tiles[2])
+    tc = (rank % tiles[0], (rank // tiles[0]) % tiles[1], rank // (tiles[0] * tiles[1]))
+    origin = (tc[0] * n, tc[1] * n, tc[2] * n)
+
+    exchanger = None
+    if world == 1:
+        # one tile = the whole periodic box: no ghost cells, stencils wrap by index like the reference
+        fl = solver.new_fluid(n, n, n, halo=0, origin=origin)
+        fill_block(solver, fl, cfg, n, origin, gN, 0)
+        tile, bounds = fl.tile(), fl.tile()
+    else:
+        from htr_solver_b200 import halo as halo_mod
+        fl = solver.new_fluid(n, n, n, halo=halo_mod.HALO, origin=origin)
+        fill_block(solver, fl, cfg, n, origin, gN, halo_mod.HALO)
+        exchanger = halo_mod.HaloExchanger(solver, fl, tiles, tc, rank, world)
+        tile = fl.tile()
+        bounds = htr.Rect.make((-2 ** 40,) * 3, (2 ** 40,) * 3)     # ghosts are resident: never wrap
+    # shock sensors once (per time step in the reference, src/prometeo.rg:1356)
+    if scheme == "Hybrid":
+        if exchanger is not None:
+            exchanger.sensors(1.0)
+        else:
+            solver.UpdateDucrosSensor(fl, 1.0)
+            for d in range(3):
+                solver.UpdateShockSensor(fl, d)
+    torch.cuda.synchronize()
+    smooth = float(fl.interior("shockSensorX").float().mean().item()) if scheme == "Hybrid" else None
+
+    def step():
+        if exchanger is not None:
+            exchanger.rhs(scheme, diffusion, chemistry, (1.0, 0.0), 1e-3)
+        else:
+            solver.UpdateDerivatives(fl, scheme, diffusion, chemistry, (1.0, 0.0), 1e-3, tile=tile, bounds=bounds)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    cells_rank = n ** 3
+    value = cells_rank * world * args.steps / (ms * 1e-3)
+
+    # ---- per-kernel durations (CUDA events on the launching stream) for the dominant-kernel roofline ----
+    kern = {}
+    if rank == 0:
+        def timed(label, fn, reps=3):
+            ts = []
+            for _ in range(reps):
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(); fn(); b.record(); torch.cuda.synchronize()
+                ts.append(a.elapsed_time(b))
+            kern[label] = float(np.mean(ts))
+        for d in (2, 1, 0):
+            timed(f"euler_{'xyz'[d]}", lambda d=d: solver.UpdateUsingEulerFlux(fl, scheme, d, (1.0, 0.0), 1e-3, tile=tile, bounds=bounds))
+        if diffusion:
+            for d in (2, 1, 0):
+                timed(f"diffusion_{'xyz'[d]}", lambda d=d: solver.UpdateUsingDiffusionFlux(fl, d, tile=tile, bounds=bounds))
+        if chemistry:
+            timed("chem_source", lambda: solver.AddChemistrySources(fl, tile=tile))
+    if world > 1:
+        dist.barrier()
+
+    # ---- end to end through the host-buffer C ABI (pinned host state in, Conserved_t out) ----
+    e2e = None
+    if rank == 0 or world > 1:
+        try:
+            hl = fl if world == 1 else solver.new_fluid(n, n, n, halo=0, origin=(0, 0, 0))
+            if world > 1:      # e2e at N>1: every rank drives its own periodic block through the host API
+                fill_block(solver, hl, cfg, n, (0, 0, 0), (n, n, n), 0)
+            hC = torch.empty((n, n, n, neq), dtype=torch.float64).pin_memory()
+            hT = torch.empty((n, n, n), dtype=torch.float64).pin_memory()
+            hCt = torch.empty((n, n, n, neq), dtype=torch.float64).pin_memory()
+            hC.copy_(hl.t["Conserved"]); hT.copy_(hl.t["temperature"])
+            torch.cuda.synchronize()
+            ke = max(1, min(args.steps, args.e2e_steps))
+            solver.HostRHS(hl, scheme, hC, hT, hCt, diffusion=diffusion, chemistry=chemistry, deltaTime=1e-3)   # warm-up
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            a.record()
+            for _ in range(ke):
+                solver.HostRHS(hl, scheme, hC, hT, hCt, diffusion=diffusion, chemistry=chemistry, deltaTime=1e-3)
+            b.record()
+            barrier()
+            ems = a.elapsed_time(b)
+            if world > 1:
+                t = torch.tensor([ems], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                ems = float(t.item())
+            h2d = 8 * cells_rank * (neq * (2 if (nspec > 1 and scheme != "SkewSymmetric") else 1) + 1)
+            d2h = 8 * cells_rank * (neq + 1)
+            e2e = {"value": cells_rank * world * ke / (ems * 1e-3), "unit": "cell-updates/s",
+                   "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": ke, "ms_per_step": ems / ke,
+                   "checksum": float(hCt.view(-1)[:: max(1, hCt.numel() // 4096)].abs().sum().item()),
+                   "includes": "H2D Conserved(+old)+T, UpdatePrimitiveFromConserved, UpdatePropertiesFromPrimitive, sensors, UpdateDerivatives, D2H Conserved_t+T"}
+        except Exception as ex:   # report, never silently drop
+            e2e = {"value": None, "unit": "cell-updates/s", "error": repr(ex)[:200]}
+    if rank != 0:
+        return
+
+    # ---- roofline of the dominant kernel ----
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    else:
+        peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+    roof = None
+    if kern:
+        top = max(kern, key=kern.get)
+        kind = top.split("_")[0] if not top.startswith("chem") else "chem"
+        kb = kernel_bytes(kind, nspec, scheme)
+        ach = kb * cells_rank / (kern[top] * 1e-3) / 1e9
+        B = algorithmic_bytes(nspec, scheme, diffusion, chemistry)
+        roof = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src, "kernel_ms": kern[top], "kernel_bytes_per_cell": kb,
+                "kernels_ms": kern, "rhs_bytes_per_cell": B,
+                "rhs_achieved_gbs": B * cells_rank * world * args.steps / (ms * 1e-3) / 1e9 / world,
+                "rhs_frac": B * cells_rank * args.steps / (ms * 1e-3) / 1e9 / peak}
+    launches_per_step = 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
+    if exchanger is not None:
+        launches_per_step = exchanger.launches_per_step(diffusion, chemistry)
+
+    cpu = None
+    if world == 1 and not args.no_cpu:
+        try:
+            v, desc = cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=args.cpu_budget)
+            cpu = {"value": v, "unit": "cell-updates/s", "cores": desc["cores"], "kind": desc["kind"], "sample": desc["sample"],
+                   "host_cpus": desc["host_cpus"]}
+        except Exception as ex:
+            cpu = {"value": None, "unit": "cell-updates/s", "error": repr(ex)[:200]}
+
+    line = {"metric": "fp64 RHS cell-updates/s", "value": value, "unit": "cell-updates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": name, "source": src, "mixture": cfg["type"], "scheme": scheme, "diffusion": diffusion,
+                       "chemistry": chemistry, "grid_per_gpu": [n, n, n], "global_grid": list(gN), "tiles": list(tiles),
+                       "smooth_fraction": smooth, "l2": "inputs larger than L2 (no flush needed)" if n >= 128 else "inputs may fit L2",
+                       "halo": "none (periodic wrap by index)" if world == 1 else "3 ghost planes, NCCL send/recv per step"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
+            "roofline": roof, "cpu_baseline": cpu, "build": solver.L.htr_build_info().decode()}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--n", type=int, default=0, help="override cells per direction per GPU (debugging only)")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_gpu(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

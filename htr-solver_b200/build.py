@@ -13,8 +13,15 @@ FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-shared", "--
          "-ccbin", "/usr/bin/g++"]
 
 
-def lib_path(mix):
-    return os.path.join(HERE, f"libhtr_b200_{mix}.so")
+# variants: "" = production (FMA contraction on, nvcc default, like the reference's own GPU build);
+# "strict" = -fmad=false -DHTR_EXACT_POW: no contraction, libdevice pow -- operation-for-operation
+# comparable with the reference's CPU tasks; used by the parity tests to separate rounding
+# from logic.
+VARIANTS = {"": [], "strict": ["-fmad=false", "-DHTR_EXACT_POW", "-DHTR_FMAD_OFF"]}
+
+
+def lib_path(mix, variant=""):
+    return os.path.join(HERE, f"libhtr_b200_{mix}{'_' + variant if variant else ''}.so")
 
 
 def sources():
@@ -25,25 +32,30 @@ def sources():
     return out
 
 
-def needs_build(mix):
-    lib = lib_path(mix)
+def needs_build(mix, variant=""):
+    lib = lib_path(mix, variant)
     if not os.path.exists(lib):
         return True
     t = os.path.getmtime(lib)
     return any(os.path.getmtime(s) > t for s in sources())
 
 
-def build(mixes=MIXES, force=False, extra=(), verbose=False):
+def build(mixes=MIXES, force=False, extra=(), verbose=False, variants=("", "strict")):
+    procs = []
     for mix in mixes:
-        if not force and not needs_build(mix):
-            continue
-        cmd = [NVCC] + ARCH + FLAGS + list(extra) + [f"-DHTR_MIX_{mix}", os.path.join(CSRC, "htr_kernels.cu"),
-                                                     "-o", lib_path(mix)]
-        if verbose:
-            cmd.insert(1, "-Xptxas=-v")
-            print(" ".join(cmd))
-        subprocess.check_call(cmd)
-    return [lib_path(m) for m in mixes]
+        for var in variants:
+            if not force and not needs_build(mix, var):
+                continue
+            cmd = [NVCC] + ARCH + FLAGS + VARIANTS[var] + list(extra) + [f"-DHTR_MIX_{mix}", os.path.join(CSRC, "htr_kernels.cu"),
+                                                                          "-o", lib_path(mix, var)]
+            if verbose:
+                cmd.insert(1, "-Xptxas=-v")
+                print(" ".join(cmd))
+            procs.append((cmd, subprocess.Popen(cmd)))
+    for cmd, p in procs:
+        if p.wait() != 0:
+            raise subprocess.CalledProcessError(p.returncode, cmd)
+    return [lib_path(m, v) for m in mixes for v in variants]
 
 
 if __name__ == "__main__":
@@ -51,6 +63,7 @@ if __name__ == "__main__":
     ap.add_argument("--mix", nargs="*", default=MIXES)
     ap.add_argument("--force", action="store_true")
     ap.add_argument("-v", action="store_true")
+    ap.add_argument("--variants", nargs="*", default=["", "strict"])
     ap.add_argument("extra", nargs="*")
     a = ap.parse_args()
-    print(build(a.mix, a.force, a.extra, a.v))
+    print(build(a.mix, a.force, a.extra, a.v, a.variants))

@@ -64,15 +64,17 @@ class HTRError(RuntimeError):
 _LIBS = {}
 
 
-def lib_path(mix):
-    return os.path.join(HERE, f"libhtr_b200_{mix}.so")
+def lib_path(mix, variant=""):
+    return os.path.join(HERE, f"libhtr_b200_{mix}{'_' + variant if variant else ''}.so")
 
 
-def load_library(mix):
-    """dlopen libhtr_b200_<Mix>.so; raises if it has not been built (no fallback)."""
-    if mix in _LIBS:
-        return _LIBS[mix]
-    path = lib_path(mix)
+def load_library(mix, variant=""):
+    """dlopen libhtr_b200_<Mix>[_strict].so; raises if it has not been built (no fallback).
+    variant "strict" = built without FMA contraction and with libdevice pow (parity debugging)."""
+    key = (mix, variant)
+    if key in _LIBS:
+        return _LIBS[key]
+    path = lib_path(mix, variant)
     if not os.path.exists(path):
         raise HTRError(f"{path} not found: build it with `python htr-solver_b200/build.py` "
                        "(there is no CPU or PyTorch fallback)")
@@ -94,8 +96,9 @@ def load_library(mix):
     L.htr_update_conserved_from_primitive.argtypes = [vp, vp, vp]
     L.htr_max_spectral_radius.argtypes = [vp, vp, vp, vp]
     L.htr_rhs.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
+    L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
     assert L.htr_mixture_name().decode() == mix
-    _LIBS[mix] = L
+    _LIBS[key] = L
     return L
 
 
@@ -188,11 +191,11 @@ class Fluid:
 class Solver:
     """The reference's leaf tasks for one mixture, on the current CUDA device."""
 
-    def __init__(self, mix_cfg):
+    def __init__(self, mix_cfg, variant=""):
         import torch
         self.torch = torch
         self.mix = mix_cfg["type"]
-        self.L = load_library(self.mix)
+        self.L = load_library(self.mix, variant)
         self.nspec = self.L.htr_nspec()
         self.neq = self.L.htr_neq()
         self.mix_bytes = mixture_bytes(self.L, mix_cfg)
@@ -268,3 +271,13 @@ class Solver:
         t, b = self._rects(fl, tile, bounds)
         self._check(self.L.htr_rhs(SCHEMES[scheme], int(diffusion), int(chemistry), C.byref(fl.struct()), t, b,
                                    RK_coeffs[0], RK_coeffs[1], deltaTime, self._stream()), "htr_rhs")
+
+    # host-buffer stage: torch CPU (pinned) tensors in, Conserved_t out; see htr_host_rhs in include/htr_b200.h
+    def HostRHS(self, fl, scheme, h_Conserved, h_temperature, h_Conserved_t, h_Conserved_old=None, diffusion=True,
+                chemistry=False, update_sensors=True, vorticityScale=1.0, RK_coeffs=(1.0, 0.0), deltaTime=0.0):
+        t, b = self._rects(fl, None, None)
+        old = C.c_void_p(h_Conserved_old.data_ptr()) if h_Conserved_old is not None else C.c_void_p(0)
+        self._check(self.L.htr_host_rhs(SCHEMES[scheme], int(diffusion), int(chemistry), int(update_sensors), vorticityScale,
+                                        C.byref(fl.struct()), t, b, C.c_void_p(h_Conserved.data_ptr()), old,
+                                        C.c_void_p(h_temperature.data_ptr()), C.c_void_p(h_Conserved_t.data_ptr()),
+                                        RK_coeffs[0], RK_coeffs[1], deltaTime, self._stream()), "htr_host_rhs")

@@ -478,4 +478,49 @@ int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const 
    return rc;
 }
 
+// ---- host-buffer entry point (what a host-resident caller binds) ------------------------------
+// The solver state a host owns is Conserved (+ the previous temperature, the Newton guess); every
+// other field the RHS reads is derived from it on the device.  One call = H2D of the state,
+// UpdatePrimitiveFromConserved + UpdatePropertiesFromPrimitive (src/prometeo.rg:450-471),
+// [sensors], UpdateDerivatives, D2H of Conserved_t.  `f` is a device workspace whose tile is dense
+// ([z][y][x][comp], no halo), metrics and node types already resident.
+static bool denseField(const htr_acc &a, const htr_rect &t, int64_t elemBytes) {
+   const int64_t nx = t.hi[0] - t.lo[0] + 1, ny = t.hi[1] - t.lo[1] + 1;
+   return a.stride[0] == elemBytes && a.stride[1] == elemBytes*nx && a.stride[2] == elemBytes*nx*ny;
+}
+static void *cellPtr(const htr_acc &a, const htr_rect &t) {
+   return static_cast<char*>(a.base) + t.lo[0]*a.stride[0] + t.lo[1]*a.stride[1] + t.lo[2]*a.stride[2];
+}
+
+int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, double vorticityScale,
+                 const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds,
+                 const double *h_Conserved, const double *h_Conserved_old, double *h_temperature,
+                 double *h_Conserved_t, double RK0, double RK1, double deltaTime, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds || !h_Conserved || !h_temperature || !h_Conserved_t) return HTR_EINVAL;
+   if (!denseField(f->Conserved, *tile, 8*nEq) || !denseField(f->Conserved_t, *tile, 8*nEq) ||
+       !denseField(f->temperature, *tile, 8) || !denseField(f->Conserved_old, *tile, 8*nEq)) return HTR_EINVAL;
+   cudaStream_t st = (cudaStream_t)stream;
+   const size_t cells = (size_t)(tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
+   cudaError_t e;
+   if ((e = cudaMemcpyAsync(cellPtr(f->Conserved, *tile), h_Conserved, cells*8*nEq, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuerr(e);
+   if (nSpec > 1 && scheme != HTR_SCHEME_SKEWSYMMETRIC) {
+      const double *src = h_Conserved_old ? h_Conserved_old : h_Conserved;
+      if ((e = cudaMemcpyAsync(cellPtr(f->Conserved_old, *tile), src, cells*8*nEq, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuerr(e);
+   }
+   if ((e = cudaMemcpyAsync(cellPtr(f->temperature, *tile), h_temperature, cells*8, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuerr(e);
+   int rc;
+   if ((rc = htr_update_primitive_from_conserved(f, tile, stream)) != HTR_OK) return rc;
+   if ((rc = htr_update_properties_from_primitive(f, tile, stream)) != HTR_OK) return rc;
+   if (update_sensors && scheme == HTR_SCHEME_HYBRID) {
+      if ((rc = htr_ducros_sensor(f, tile, bounds, vorticityScale, stream)) != HTR_OK) return rc;
+      for (int d = 0; d < 3; d++)
+         if ((rc = htr_shock_sensor(d, f, tile, bounds, stream)) != HTR_OK) return rc;
+   }
+   if ((rc = htr_rhs(scheme, diffusion, chemistry, f, tile, bounds, RK0, RK1, deltaTime, stream)) != HTR_OK) return rc;
+   if ((e = cudaMemcpyAsync(h_Conserved_t, cellPtr(f->Conserved_t, *tile), cells*8*nEq, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuerr(e);
+   if ((e = cudaMemcpyAsync(h_temperature, cellPtr(f->temperature, *tile), cells*8, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuerr(e);
+   return HTR_OK;
+}
+
 } // extern "C"

@@ -20,7 +20,7 @@ AIR_SPECIES = ["N2", "O2", "NO", "N", "O"]
 
 
 def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=0.0, species_wave=0.0,
-                 front=0.0, dtype=np.float64):
+                 front=0.0, dtype=np.float64, zslab=None, offset=(0, 0, 0), global_n=None):
     """Host fields of an (nx,ny,nz)=n periodic box.  Returns dict name -> array [z][y][x](comp).
 
     stretch > 0      multiplies the metrics by 1 + stretch*sin(coordinate): a smooth non-uniform grid
@@ -29,16 +29,21 @@ def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=
                      (steep gradients: exercises the nonlinear TENO weights and the shock sensor)
     """
     nx, ny, nz = (n, n, n) if np.isscalar(n) else n
+    gx, gy, gz = (nx, ny, nz) if global_n is None else ((global_n,) * 3 if np.isscalar(global_n) else global_n)
     multi = mix_cfg["type"] != "ConstPropMix"
     nspec = 5 if multi else 1
     if p0 is None:
         p0, T0, U = (1.0, 1.0, 0.002634364032587426) if multi else (100.0, 100.0, 1.0)
-    x = (np.arange(nx) + 0.5) * width / nx
-    y = (np.arange(ny) + 0.5) * width / ny
-    z = (np.arange(nz) + 0.5) * width / nz
+    # (nx,ny,nz) is this block of a (gx,gy,gz) global box, starting at cell `offset`;
+    # zslab=(k0,k1) restricts the output to local planes k0..k1-1 (slab-wise generation of big boxes)
+    k0, k1 = (0, nz) if zslab is None else zslab
+    x = (np.arange(nx) + offset[0] + 0.5) * width / gx
+    y = (np.arange(ny) + offset[1] + 0.5) * width / gy
+    z = (np.arange(k0, k1) + offset[2] + 0.5) * width / gz
+    nz = k1 - k0
     Z, Y, X = np.meshgrid(z, y, x, indexing="ij")
     f = {}
-    for d, (nn, c) in enumerate(((nx, X), (ny, Y), (nz, Z))):
+    for d, (nn, c) in enumerate(((gx, X), (gy, Y), (gz, Z))):
         m = (nn / width) * (1.0 + stretch * np.sin(c + 0.3 * d))
         for kind in "eds":
             f[("dcsi_", "deta_", "dzet_")[d] + kind] = np.ascontiguousarray(m * (1.0 + 0.01 * stretch * "eds".index(kind)))
@@ -51,7 +56,7 @@ def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=
     P = p0 + rho0 * U ** 2 / 16.0 * (np.cos(2 * Z) + 2.0) * (np.cos(2 * X) + np.cos(2 * Y))
     T = P / (rho0 * R)
     if front > 0.0:
-        s = np.tanh((X - 0.5 * width) * 8.0 / width * nx / 32.0) * np.cos(Y) * np.cos(Z)
+        s = np.tanh((X - 0.5 * width) * 8.0 / width * gx / 32.0) * np.cos(Y) * np.cos(Z)
         T = T * (1.0 + front * s)
         P = P * (1.0 + 0.5 * front * s)
     Xi = np.zeros((nz, ny, nx, nspec))

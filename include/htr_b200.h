@@ -112,6 +112,18 @@ int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_
 int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
             const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
 
+/* ---- host-buffer stage (the call a host-resident driver binds) ----
+ * h_* are HOST pointers (pinned for full copy bandwidth), dense [z][y][x][comp] over `tile`.
+ * Copies Conserved (and Conserved_old for the multispecies limiter; NULL = same as Conserved) and the
+ * previous temperature to the device workspace `f`, recovers primitives and properties
+ * (src/prometeo.rg:450-471), optionally refreshes the shock sensors (src/prometeo.rg:1356), evaluates
+ * UpdateDerivatives and copies Conserved_t (and the converged temperature) back.  Asynchronous on
+ * `stream`; synchronise it before reading h_Conserved_t. */
+int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, double vorticityScale,
+                 const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds,
+                 const double *h_Conserved, const double *h_Conserved_old, double *h_temperature,
+                 double *h_Conserved_t, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

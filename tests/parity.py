@@ -57,3 +57,25 @@ def solver_tol_ok(a, b):
     abs(d) <= max(1e-10*abs(ref), 1e-12)."""
     a = np.asarray(a); b = np.asarray(b)
     return bool(np.all(np.abs(a - b) <= np.maximum(1e-10 * np.abs(b), 1e-12)))
+
+
+def euler_scale(f, d):
+    """Magnitude of the operands of the Euler flux difference, per conserved component:
+    m_e * (|u_n| + c) * |U_i|  (+ m_e * p for momentum, (|u_n|+c) * (rhoE + p) for energy).
+    Conserved_t[i] = m*(F+ - F-) is a difference of two numbers of this size, so its absolute
+    rounding floor is eps * scale even where the divergence itself vanishes (e.g. the z-flux of
+    the Taylor-Green box, w = 0).  The parity error of a flux RHS is reported relative to it."""
+    m = f[("dcsi_e", "deta_e", "dzet_e")[d]].max()
+    lam = (np.abs(f["velocity"][..., d]) + f["SoS"]).max()
+    U = np.abs(f["Conserved"]).reshape(-1, f["Conserved"].shape[-1]).max(axis=0)
+    n = f["Conserved"].shape[-1]
+    s = m * lam * U
+    p = f["pressure"].max()
+    s[n - 4:n - 1] = np.maximum(s[n - 4:n - 1], m * p)
+    s[n - 1] = m * lam * (U[n - 1] + p)
+    return s
+
+
+def scaled_err(got, ref, scale):
+    num = np.abs(got - ref).reshape(-1, got.shape[-1]).max(axis=0)
+    return float(np.max(num / scale))
