@@ -138,19 +138,27 @@ def test_chemistry_sources():
     assert rel_err(got[..., :5], f["Conserved_t"][..., :5]) <= TOL_CHEM
 
 
-def test_update_chemistry():
+@pytest.mark.parametrize("variant", ["", "strict"], ids=["prod", "strict"])
+def test_update_chemistry(variant):
     o = oracle_for(AIR)
     f = host_state(o, (8, 6, 4), AIR, species_wave=1.0, T0=9.0)
     f["Conserved_t"][...] = 0.0
-    s = htr.Solver(AIR)
+    s = htr.Solver(AIR, variant=variant)
     fl = to_device(s, f)
     dt = 1e-3
+    before = f["Conserved"].copy()
     o.update_chemistry(f, dt)
     s.UpdateChemistry(fl, dt)
     got = fl.download(["Conserved", "temperature", "Conserved_t_old"])
-    # adaptive integrator with TOL=1e-10 per step: agreement to the integrator's own tolerance
-    assert rel_err(got["Conserved"], f["Conserved"]) <= 1e-8
-    assert rel_err(got["temperature"], f["temperature"]) <= 1e-8
+    assert rel_err(before[..., :5], f["Conserved"][..., :5]) > 1e-3, "chemistry must be active in this test"
+    # the adaptive integrator controls its local error to TOL=1e-10 (src/Utils/math_utils.hpp:391) and its
+    # finite-difference Jacobian amplifies last-digit differences of exp/log/pow by 1/h = 1e6:
+    # agreement is to the integrator's tolerance class, not to round-off
+    # `temperature` leaves the task as the Newton iterate of the LAST rhs() call, i.e. at the third-stage
+    # state of the last Rosenbrock step (src/prometeo_chem.hpp:66-87): it depends on the adaptive step
+    # sequence (dtNext ~ errmax^-1/4, errmax = noise-level error / 1e-10) and is only a Newton guess.
+    eC, eT = rel_err(got["Conserved"], f["Conserved"]), rel_err(got["temperature"], f["temperature"])
+    assert eC <= 1e-9 and eT <= 1e-5, (eC, eT)
 
 
 @pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "SkewSymmetric", False, {}), (CP, "Hybrid", False, {"front": 0.3}),
@@ -168,5 +176,11 @@ def test_full_rhs(cfg, scheme, chem, kw):
     s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=(1.0, 0.0), deltaTime=1e-3)
     got = fl.download(["Conserved_t"])["Conserved_t"]
     scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
+    if chem:   # the source term has its own magnitude (it can dwarf the fluxes of a slow flow)
+        ref = f["Conserved_t"].copy()
+        f["Conserved_t"][...] = 0.0
+        o.add_chemistry_sources(f)
+        scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
+        f["Conserved_t"][...] = ref
     e = scaled_err(got, f["Conserved_t"], scale)
     assert e <= (TOL_CHEM if chem else TOL_FLUX), e
