@@ -1,0 +1,193 @@
+"""Block decomposition and ghost-plane exchange for the RHS hot path.
+
+Mirrors what `prometeo_partitioner` declares and Legion/Realm executes in the reference
+(src/prometeo_partitioner.rg:436-446 tiling, :1107-1352 ghost partitions; one instance per tile
+holding interior + ghosts, src/prometeo_mapper.cc:1142-1204): the global box is cut into
+tiles=[tx,ty,tz] equal blocks, one per GPU; every block keeps HALO = 3 ghost planes per side
+(the Euler stencil reach, partitioner.rg:1239-1252).  Ghost data moves with NCCL send/recv
+(torch.distributed P2P) in three phases x -> y -> z whose slabs include the ghosts received in the
+earlier phases, so edges and corners (needed by the transverse velocity gradients of the
+diffusion flux, partitioner.rg:1287-1301) arrive without diagonal messages.  Periodic wrap =
+neighbour index modulo the tile count; a direction with one tile wraps onto the block itself
+(local copy).
+
+What is exchanged per RHS evaluation: Conserved and temperature only (80 B/cell for AirMix);
+primitives and properties of the ghost cells are recomputed locally by the same kernels.  The
+exchanged temperature is the owner's converged value, so the ghost Newton solve returns it
+unchanged and ghost data are bit-identical with the owner's.
+"""
+import numpy as np
+
+HALO = 3
+
+
+def tile_coords(rank, tiles):
+    return (rank % tiles[0], (rank // tiles[0]) % tiles[1], rank // (tiles[0] * tiles[1]))
+
+
+def rank_of(tc, tiles):
+    return (tc[0] % tiles[0]) + tiles[0] * ((tc[1] % tiles[1]) + tiles[1] * (tc[2] % tiles[2]))
+
+
+def neighbours(rank, tiles):
+    """[(minus_rank, plus_rank)] per direction, periodic."""
+    tc = tile_coords(rank, tiles)
+    out = []
+    for d in range(3):
+        lo = list(tc); hi = list(tc)
+        lo[d] -= 1; hi[d] += 1
+        out.append((rank_of(lo, tiles), rank_of(hi, tiles)))
+    return out
+
+
+def phase_slices(n, d, h=HALO):
+    """Index slices (z, y, x order, into arrays with h ghost planes per side) of phase d:
+    returns (send_lo, send_hi, recv_lo, recv_hi).  Dimensions < d span interior+ghosts (already
+    exchanged), dimensions > d span the interior only."""
+    def span(dd):
+        return slice(0, n[dd] + 2 * h) if dd < d else slice(h, h + n[dd])
+
+    def mk(sl_d):
+        s = [span(0), span(1), span(2)]
+        s[d] = sl_d
+        return (s[2], s[1], s[0])          # arrays are [z][y][x]
+    send_lo = mk(slice(h, 2 * h))                       # first h interior planes  -> minus neighbour's high ghosts
+    send_hi = mk(slice(n[d], n[d] + h))                 # last h interior planes   -> plus neighbour's low ghosts
+    recv_lo = mk(slice(0, h))
+    recv_hi = mk(slice(n[d] + h, n[d] + 2 * h))
+    return send_lo, send_hi, recv_lo, recv_hi
+
+
+def exchange(tensors, n, rank, tiles, dist=None, h=HALO):
+    """Fills the ghost planes of every tensor in `tensors` ([z][y][x](comp), h ghosts per side).
+    Runs on whatever stream / device the tensors live on; `dist` = torch.distributed (None or
+    world 1: all wraps are local)."""
+    import torch
+    nb = neighbours(rank, tiles)
+    for d in range(3):
+        s_lo, s_hi, r_lo, r_hi = phase_slices(n, d, h)
+        if tiles[d] == 1:
+            for t in tensors:
+                t[r_hi].copy_(t[s_lo])
+                t[r_lo].copy_(t[s_hi])
+            continue
+        minus, plus = nb[d]
+        # one packed message per direction and side
+        out_lo = torch.cat([t[s_lo].reshape(-1).view(torch.uint8) for t in tensors])
+        out_hi = torch.cat([t[s_hi].reshape(-1).view(torch.uint8) for t in tensors])
+        in_lo = torch.empty_like(out_hi)    # from the minus neighbour: its high planes
+        in_hi = torch.empty_like(out_lo)
+        if tiles[d] == 2:
+            # both neighbours are the same rank: tag by ordering (send lo first, receive hi-side first)
+            ops = [dist.P2POp(dist.isend, out_lo, minus), dist.P2POp(dist.isend, out_hi, plus),
+                   dist.P2POp(dist.irecv, in_hi, plus), dist.P2POp(dist.irecv, in_lo, minus)]
+        else:
+            ops = [dist.P2POp(dist.isend, out_lo, minus), dist.P2POp(dist.isend, out_hi, plus),
+                   dist.P2POp(dist.irecv, in_hi, plus), dist.P2POp(dist.irecv, in_lo, minus)]
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        off_lo = off_hi = 0
+        for t in tensors:
+            v = t[r_lo]
+            nb_ = v.numel() * v.element_size()
+            v.copy_(in_lo[off_lo:off_lo + nb_].view(t.dtype).view(v.shape)); off_lo += nb_
+            v = t[r_hi]
+            nb_ = v.numel() * v.element_size()
+            v.copy_(in_hi[off_hi:off_hi + nb_].view(t.dtype).view(v.shape)); off_hi += nb_
+
+
+def shell_rects(origin, n, h=HALO):
+    """The ghost region as 6 disjoint boxes (global coordinates, inclusive): x slabs over the interior
+    y,z; y slabs over x incl. ghosts; z slabs over x,y incl. ghosts."""
+    o = origin
+    lo = [o[0], o[1], o[2]]; hi = [o[0] + n[0] - 1, o[1] + n[1] - 1, o[2] + n[2] - 1]
+    rects = []
+    for d in range(3):
+        a = [lo[k] - (h if k < d else 0) for k in range(3)]
+        b = [hi[k] + (h if k < d else 0) for k in range(3)]
+        r1a, r1b = list(a), list(b); r1a[d] = lo[d] - h; r1b[d] = lo[d] - 1
+        r2a, r2b = list(a), list(b); r2a[d] = hi[d] + 1; r2b[d] = hi[d] + h
+        rects += [(tuple(r1a), tuple(r1b)), (tuple(r2a), tuple(r2b))]
+    return rects
+
+
+def boundary_rects(origin, n, w=HALO):
+    """Interior cells within w of the block boundary as 6 disjoint boxes + the inner box that needs
+    no ghost data.  Returns (inner, [shell boxes]); boxes may be empty (lo > hi) for thin blocks."""
+    o = origin
+    lo = [o[0], o[1], o[2]]; hi = [o[0] + n[0] - 1, o[1] + n[1] - 1, o[2] + n[2] - 1]
+    inner = (tuple(l + w for l in lo), tuple(u - w for u in hi))
+    shells = []
+    a, b = list(lo), list(hi)
+    for d in (2, 1, 0):            # peel z slabs (full x,y), then y slabs, then x slabs
+        s1a, s1b = list(a), list(b); s1b[d] = min(lo[d] + w - 1, hi[d])
+        s2a, s2b = list(a), list(b); s2a[d] = max(hi[d] - w + 1, s1b[d] + 1)
+        shells += [(tuple(s1a), tuple(s1b)), (tuple(s2a), tuple(s2b))]
+        a[d] = lo[d] + w; b[d] = hi[d] - w
+    return inner, shells
+
+
+class HaloExchanger:
+    """Per-rank driver of one block: ghost exchange overlapped with the interior RHS."""
+
+    def __init__(self, solver, fl, tiles, tc, rank, world):
+        import torch
+        import torch.distributed as dist
+        from .core import Rect
+        self.torch, self.dist, self.Rect = torch, dist, Rect
+        self.s, self.fl, self.tiles, self.tc, self.rank, self.world = solver, fl, tuple(tiles), tuple(tc), rank, world
+        self.n = (fl.nx, fl.ny, fl.nz)
+        assert fl.halos() == (HALO, HALO, HALO)
+        self.comm = torch.cuda.Stream()
+        self.ghost_boxes = [Rect.make(a, b) for a, b in shell_rects(fl.origin, self.n)]
+        inner, shells = boundary_rects(fl.origin, self.n)
+        self.inner = Rect.make(*inner)
+        self.shells = [Rect.make(a, b) for a, b in shells if all(x <= y for x, y in zip(a, b))]
+        self.nowrap = Rect.make((-2 ** 40,) * 3, (2 ** 40,) * 3)
+
+    # ghost planes of the state, then ghost primitives/properties (on the current stream)
+    def exchange_state(self):
+        fl = self.fl
+        exchange([fl.t["Conserved"], fl.t["temperature"]], self.n, self.rank, self.tiles, self.dist)
+        for box in self.ghost_boxes:
+            self.s.UpdatePrimitiveFromConserved(fl, tile=box)
+            self.s.UpdatePropertiesFromPrimitive(fl, tile=box)
+
+    def sensors(self, vorticityScale):
+        """UpdateShockSensors (src/prometeo_sensor.rg:90-124) with the two ghost exchanges it implies."""
+        fl, s = self.fl, self.s
+        self.exchange_state()
+        s.UpdateDucrosSensor(fl, vorticityScale, bounds=self.nowrap)
+        exchange([fl.t["DucrosSensor"]], self.n, self.rank, self.tiles, self.dist)
+        for d in range(3):
+            s.UpdateShockSensor(fl, d, bounds=self.nowrap)
+        exchange([fl.t["shockSensorX"], fl.t["shockSensorY"], fl.t["shockSensorZ"]], self.n, self.rank, self.tiles, self.dist)
+
+    def _fluxes(self, box, scheme, diffusion, rk, dt):
+        fl, s = self.fl, self.s
+        for d in (2, 1, 0):
+            s.UpdateUsingEulerFlux(fl, scheme, d, rk, dt, tile=box, bounds=self.nowrap)
+        if diffusion:
+            for d in (2, 1, 0):
+                s.UpdateUsingDiffusionFlux(fl, d, tile=box, bounds=self.nowrap)
+
+    def rhs(self, scheme, diffusion, chemistry, rk, dt):
+        """One UpdateDerivatives pass of the block.  The ghost exchange runs on a side stream while the
+        cells that need no ghost data are updated; the boundary shells follow.  Every cell belongs to
+        exactly one box and each box runs the reference's order (chem, Euler z,y,x, diffusion z,y,x)."""
+        torch, fl, s = self.torch, self.fl, self.s
+        main = torch.cuda.current_stream()
+        self.comm.wait_stream(main)
+        with torch.cuda.stream(self.comm):
+            self.exchange_state()
+        fl.t["Conserved_t"].zero_()
+        if chemistry:
+            s.AddChemistrySources(fl)
+        self._fluxes(self.inner, scheme, diffusion, rk, dt)
+        main.wait_stream(self.comm)
+        for box in self.shells:
+            self._fluxes(box, scheme, diffusion, rk, dt)
+
+    def launches_per_step(self, diffusion, chemistry):
+        per_box = 3 + (3 if diffusion else 0)
+        return 1 + (1 if chemistry else 0) + per_box * (1 + len(self.shells)) + 2 * len(self.ghost_boxes)
