@@ -104,7 +104,7 @@ namespace Legion {
       static LayoutConstraintID preregister_layout(const LayoutConstraintRegistrar&) { return 0; }
    };
    template<typename T> class SumReduction {};
-   template<typename T> struct DeferredValue { T v; DeferredValue(T x = T()) : v(x) {} };
+   template<typename T> struct DeferredValue { T v; DeferredValue(T x = T()) : v(x) {} T* ptr() { return &v; } };
    template<typename T, int N> struct DeferredBuffer {};
    template<int N> struct RectInDomainIterator {};
 
@@ -118,6 +118,11 @@ namespace Legion {
       FieldAccessor(const PhysicalRegion&, FieldID) : base(0), sx(0), sy(0), sz(0) {}
       FieldAccessor(void *b, coord_t sx_, coord_t sy_, coord_t sz_) : base((char*)b), sx(sx_), sy(sy_), sz(sz_) {}
       FT& operator[](const Point<3, T> &p) const { return *(FT*)(base + p.x*sx + p.y*sy + p.z*sz); }
+      // Legion: pointer to r.lo and strides in units of field_size
+      FT* ptr(const Rect<3, T> &r, size_t strides[3], size_t field_size = sizeof(FT)) const {
+         strides[0] = sx/field_size; strides[1] = sy/field_size; strides[2] = sz/field_size;
+         return &(*this)[r.lo];
+      }
    };
    template<int PRIV, typename FT, typename T, typename A>
    struct FieldAccessor<PRIV, FT, 1, T, A> {
