@@ -337,9 +337,9 @@ def run_gpu(args, rank, world, local_rank):
                 "kernels_ms": kern, "rhs_bytes_per_cell": B,
                 "rhs_achieved_gbs": B * cells_rank * world * args.steps / (ms * 1e-3) / 1e9 / world,
                 "rhs_frac": B * cells_rank * args.steps / (ms * 1e-3) / 1e9 / peak}
-    launches_per_step = 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
+    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry)
     if exchanger is not None:
-        launches_per_step = exchanger.launches_per_step(diffusion, chemistry)
+        launches_per_step = exchanger.launches_per_step(diffusion, chemistry, scheme)
 
     cpu = None
     if world == 1 and not args.no_cpu:

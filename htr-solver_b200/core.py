@@ -57,6 +57,13 @@ def ncomp(c, nspec):
     return {0: 1, 3: 3, "S": nspec, "E": nspec + 4}[c]
 
 
+def rhs_launches(scheme, diffusion, chemistry, fast=True):
+    """Kernels one htr_rhs call launches (csrc/htr_kernels.cu: htr_rhs)."""
+    if fast and scheme in ("Hybrid", "SkewSymmetric"):
+        return 2 + 3 + (3 if diffusion else 0)       # z+chem, xy, three masked generic passes, diffusion
+    return 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
+
+
 class HTRError(RuntimeError):
     pass
 
@@ -85,6 +92,7 @@ def load_library(mix, variant=""):
     L.htr_mix_init_constprop.argtypes = [vp, d, d, d, i, d, d, d]
     L.htr_mix_init_multicomp.argtypes = [vp, d, d, d, i, C.c_char_p, vp]
     L.htr_set_mixture.argtypes = [vp, C.c_size_t]
+    L.htr_set_option.argtypes = [C.c_char_p, i]
     L.htr_euler_flux.argtypes = [i, i, vp, vp, vp, d, d, d, vp]
     L.htr_diffusion_flux.argtypes = [i, vp, vp, vp, vp]
     L.htr_ducros_sensor.argtypes = [vp, vp, vp, d, vp]
@@ -205,6 +213,10 @@ class Solver:
     def _check(self, rc, what):
         if rc != 0:
             raise HTRError(f"{what} failed with code {rc}")
+
+    def set_option(self, name, value):
+        """Library switch (htr_set_option): "fast" 1/0 = staged fast path of htr_rhs on/off."""
+        self._check(self.L.htr_set_option(name.encode(), int(value)), "htr_set_option")
 
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream().cuda_stream)

@@ -14,6 +14,7 @@
 #include "htr_euler.cuh"
 #include "htr_diffusion.cuh"
 #include "htr_pointwise.cuh"
+#include "htr_fast.cuh"
 
 namespace htr {
 
@@ -51,9 +52,12 @@ HTR_DEV void eulerFace(double *Flux, const htr_fluid &f, const Pt &p, int t, con
 }
 
 // KIND = FLUX_EULER (SCHEME selects the reconstruction) or FLUX_DIFFUSION
-template<int dir, int KIND, int SCHEME>
+// MASKED: only the cells flagged in `mask` (dense over the tile, see htr_fast.cuh) are updated and only
+// the faces they need are evaluated; a block without flagged cells returns at once.
+template<int dir, int KIND, int SCHEME, bool MASKED = false>
 __global__ void __launch_bounds__(256)
-flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep) {
+flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep,
+                       const uint8_t *__restrict__ mask = nullptr) {
    using FB = FaceBlock<dir>;
    constexpr int NT = FB::X*FB::Y*FB::Z;
    __shared__ double sF[nEq][NT];
@@ -69,8 +73,23 @@ flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B,
    const bool inCross = (dir == 0 || c.x <= tile.hi[0]) && (dir == 1 || c.y <= tile.hi[1]) && (dir == 2 || c.z <= tile.hi[2]);
    const int64_t cd = (dir == 0) ? c.x : ((dir == 1) ? c.y : c.z);
    const bool active = inCross && (cd <= tile.hi[dir]);
+   bool need = active, mine = true;
+   if (MASKED) {
+      mine = false;
+      bool next = false;
+      if (active) {
+         if (cd >= tile.lo[dir]) mine = mask[fast::maskIndex(c, tile)] != 0;
+         if (cd < tile.hi[dir]) {
+            Pt n = c;
+            ((dir == 0) ? n.x : ((dir == 1) ? n.y : n.z)) += 1;
+            next = mask[fast::maskIndex(n, tile)] != 0;
+         }
+      }
+      need = mine || next;
+      if (!__syncthreads_or(need)) return;
+   }
 
-   if (active) {
+   if (need) {
       Pt p = c;
       if (fd == 0) {
          // first minus face of the block: the face owned by the neighbour below the first cell
@@ -86,7 +105,7 @@ flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B,
       for (int i = 0; i < nEq; i++) sF[i][tid] = Flux[i];
    }
    __syncthreads();
-   if (active && fd > 0) {
+   if (active && fd > 0 && mine) {
       constexpr int below = (dir == 0) ? 1 : ((dir == 1) ? FB::X : FB::X*FB::Y);
       const double m = ld<double>((KIND == FLUX_EULER) ? m_eOf<dir>(f) : m_dOf<dir>(f), c);
       double *Ct = at<double>(f.Conserved_t, c);
@@ -105,6 +124,56 @@ static cudaError_t launchFlux(const htr_fluid &f, const htr_rect &tile, const ht
    dim3 block(FB::X, FB::Y, FB::Z);
    flux_divergence_kernel<dir, KIND, SCHEME><<<grid, block, 0, st>>>(f, tile, B, ep);
    return cudaGetLastError();
+}
+
+template<int dir, int SCHEME>
+static cudaError_t launchEulerMasked(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
+                                     const uint8_t *mask, cudaStream_t st) {
+   using FB = FaceBlock<dir>;
+   const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
+   const int C[3] = {FB::X - (dir == 0), FB::Y - (dir == 1), FB::Z - (dir == 2)};
+   dim3 grid((unsigned)((n[0] + C[0] - 1)/C[0]), (unsigned)((n[1] + C[1] - 1)/C[1]), (unsigned)((n[2] + C[2] - 1)/C[2]));
+   dim3 block(FB::X, FB::Y, FB::Z);
+   flux_divergence_kernel<dir, FLUX_EULER, SCHEME, true><<<grid, block, 0, st>>>(f, tile, B, ep, mask);
+   return cudaGetLastError();
+}
+
+// Fast path of  Conserved_t = 0 (+chem) + Euler z,y,x  for the Hybrid and SkewSymmetric schemes
+// (htr_fast.cuh) followed by the masked generic kernels for the cells it deferred.
+// `scratch` holds two mask bytes per cell of the tile.
+template<int SCHEME>
+static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
+                                   const EulerParams &ep, uint8_t *scratch, cudaStream_t st) {
+   constexpr bool HY = (SCHEME == HTR_SCHEME_HYBRID);
+   constexpr int TY = 8;
+   const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
+   uint8_t *maskZ = scratch, *maskXY = scratch + n[0]*n[1]*n[2];
+   static bool attr = false;
+   if (!attr) {
+      cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
+      cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
+      cudaFuncSetAttribute(fast::euler_xy_kernel<TY, HY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::XYTile<TY>::SMEM);
+      attr = true;
+   }
+   {
+      dim3 grid((unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1], (unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)));
+      dim3 block(fast::ZT_X, fast::ZT_Z, 1);
+      if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ);
+      else      fast::euler_z_chem_kernel<HY, false><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ);
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) return e;
+      if ((e = launchEulerMasked<2, SCHEME>(f, tile, B, ep, maskZ, st)) != cudaSuccess) return e;
+   }
+   {
+      dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TY - 2)/(TY - 1)), (unsigned)n[2]);
+      dim3 block(32, TY, 1);
+      fast::euler_xy_kernel<TY, HY><<<grid, block, fast::XYTile<TY>::SMEM, st>>>(f, tile, B, maskXY);
+      cudaError_t e = cudaGetLastError();
+      if (e != cudaSuccess) return e;
+      if ((e = launchEulerMasked<1, SCHEME>(f, tile, B, ep, maskXY, st)) != cudaSuccess) return e;
+      if ((e = launchEulerMasked<0, SCHEME>(f, tile, B, ep, maskXY, st)) != cudaSuccess) return e;
+   }
+   return cudaSuccess;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -252,6 +321,28 @@ using namespace htr;
 #endif
 
 static bool g_mix_loaded = false;
+static bool g_no_fast = false;          // htr_set_option("fast", 0): per-task kernels only (A/B testing)
+
+// Device scratch owned by the library (mask bytes of the fast path).  One buffer per stream that ever
+// asked, grown on demand; growth synchronises the device once.
+struct Scratch { cudaStream_t st; void *p; size_t bytes; };
+static Scratch g_scratch[16];
+static int g_nscratch = 0;
+static void *scratchFor(size_t bytes, cudaStream_t st) {
+   int k = -1;
+   for (int i = 0; i < g_nscratch; i++) if (g_scratch[i].st == st) { k = i; break; }
+   if (k < 0) {
+      if (g_nscratch == 16) k = 0; else { k = g_nscratch++; g_scratch[k] = {st, nullptr, 0}; }
+      if (g_scratch[k].st != st) { cudaDeviceSynchronize(); cudaFree(g_scratch[k].p); g_scratch[k] = {st, nullptr, 0}; }
+   }
+   Scratch &s = g_scratch[k];
+   if (s.bytes < bytes) {
+      if (s.p) { cudaDeviceSynchronize(); cudaFree(s.p); s.p = nullptr; s.bytes = 0; }
+      if (cudaMalloc(&s.p, bytes) != cudaSuccess) { s.p = nullptr; return nullptr; }
+      s.bytes = bytes;
+   }
+   return s.p;
+}
 
 static inline int cuerr(cudaError_t e) { return e == cudaSuccess ? HTR_OK : 1000 + (int)e; }
 static inline bool rectEmpty(const htr_rect &r) { return r.hi[0] < r.lo[0] || r.hi[1] < r.lo[1] || r.hi[2] < r.lo[2]; }
@@ -352,6 +443,12 @@ int htr_mix_init_multicomp(void *out, double LRef, double PRef, double TRef,
    memcpy(out, &m, sizeof(m));
    return HTR_OK;
 #endif
+}
+
+int htr_set_option(const char *name, int value) {
+   if (!name) return HTR_EINVAL;
+   if (strcmp(name, "fast") == 0) { g_no_fast = (value == 0); return HTR_OK; }
+   return HTR_EINVAL;
 }
 
 int htr_set_mixture(const void *mix, size_t bytes) {
@@ -463,6 +560,22 @@ int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const 
    if (!bounds) return HTR_EINVAL;
    // Reference task order (src/prometeo.rg:502-578): 0, +chem, +Euler z,y,x, +diffusion z,y,x.
    cudaStream_t st = (cudaStream_t)stream;
+   if (scheme < 0 || scheme > HTR_SCHEME_SKEWSYMMETRIC) return HTR_EINVAL;
+   if ((scheme == HTR_SCHEME_HYBRID || scheme == HTR_SCHEME_SKEWSYMMETRIC) && !g_no_fast) {
+      const int64_t cells = (tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
+      uint8_t *scratch = (uint8_t*)scratchFor((size_t)(2*cells), st);
+      if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
+      const EulerParams ep = {RK0, RK1, deltaTime};
+      cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
+         ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st)
+         : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st);
+      if (e != cudaSuccess) return cuerr(e);
+      int rc = HTR_OK;
+      if (diffusion)
+         for (int d = 2; d >= 0; d--)
+            if ((rc = htr_diffusion_flux(d, f, tile, bounds, stream)) != HTR_OK) return rc;
+      return rc;
+   }
    {  // Conserved_t = 0 over the tile (RK.InitializeTimeDerivatives, src/prometeo_rk.rg:61-87)
       zero_rhs_kernel<<<blocksFor(*tile, 128), 128, 0, st>>>(*f, *tile);
       cudaError_t e = cudaGetLastError();

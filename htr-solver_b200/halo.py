@@ -111,19 +111,26 @@ def shell_rects(origin, n, h=HALO):
     return rects
 
 
+# Shell thickness per direction (x, y, z): at least the stencil reach (HALO); wider where the staged
+# kernels' tiles (32 x 8 cells in-plane, 16 planes in z: csrc/htr_fast.cuh) would otherwise run nearly empty.
+SHELL_W = (32, 8, 16)
+
+
 def boundary_rects(origin, n, w=HALO):
-    """Interior cells within w of the block boundary as 6 disjoint boxes + the inner box that needs
-    no ghost data.  Returns (inner, [shell boxes]); boxes may be empty (lo > hi) for thin blocks."""
+    """Interior cells within w (scalar or per-direction) of the block boundary as 6 disjoint boxes + the
+    inner box that needs no ghost data.  Returns (inner, [shell boxes]); boxes may be empty (lo > hi)."""
     o = origin
+    w = (w, w, w) if np.isscalar(w) else tuple(w)
+    assert min(w) >= HALO
     lo = [o[0], o[1], o[2]]; hi = [o[0] + n[0] - 1, o[1] + n[1] - 1, o[2] + n[2] - 1]
-    inner = (tuple(l + w for l in lo), tuple(u - w for u in hi))
+    inner = (tuple(l + wd for l, wd in zip(lo, w)), tuple(u - wd for u, wd in zip(hi, w)))
     shells = []
     a, b = list(lo), list(hi)
     for d in (2, 1, 0):            # peel z slabs (full x,y), then y slabs, then x slabs
-        s1a, s1b = list(a), list(b); s1b[d] = min(lo[d] + w - 1, hi[d])
-        s2a, s2b = list(a), list(b); s2a[d] = max(hi[d] - w + 1, s1b[d] + 1)
+        s1a, s1b = list(a), list(b); s1b[d] = min(lo[d] + w[d] - 1, hi[d])
+        s2a, s2b = list(a), list(b); s2a[d] = max(hi[d] - w[d] + 1, s1b[d] + 1)
         shells += [(tuple(s1a), tuple(s1b)), (tuple(s2a), tuple(s2b))]
-        a[d] = lo[d] + w; b[d] = hi[d] - w
+        a[d] = lo[d] + w[d]; b[d] = hi[d] - w[d]
     return inner, shells
 
 
@@ -140,7 +147,8 @@ class HaloExchanger:
         assert fl.halos() == (HALO, HALO, HALO)
         self.comm = torch.cuda.Stream()
         self.ghost_boxes = [Rect.make(a, b) for a, b in shell_rects(fl.origin, self.n)]
-        inner, shells = boundary_rects(fl.origin, self.n)
+        w = tuple(min(SHELL_W[d], max(HALO, self.n[d] // 4)) for d in range(3))
+        inner, shells = boundary_rects(fl.origin, self.n, w)
         self.inner = Rect.make(*inner)
         self.shells = [Rect.make(a, b) for a, b in shells if all(x <= y for x, y in zip(a, b))]
         self.nowrap = Rect.make((-2 ** 40,) * 3, (2 ** 40,) * 3)
@@ -180,14 +188,12 @@ class HaloExchanger:
         self.comm.wait_stream(main)
         with torch.cuda.stream(self.comm):
             self.exchange_state()
-        fl.t["Conserved_t"].zero_()
-        if chemistry:
-            s.AddChemistrySources(fl)
-        self._fluxes(self.inner, scheme, diffusion, rk, dt)
+        # each box is one htr_rhs call (0 + chem + Euler z,y,x + diffusion z,y,x over the box)
+        s.UpdateDerivatives(fl, scheme, diffusion, chemistry, rk, dt, tile=self.inner, bounds=self.nowrap)
         main.wait_stream(self.comm)
         for box in self.shells:
-            self._fluxes(box, scheme, diffusion, rk, dt)
+            s.UpdateDerivatives(fl, scheme, diffusion, chemistry, rk, dt, tile=box, bounds=self.nowrap)
 
-    def launches_per_step(self, diffusion, chemistry):
-        per_box = 3 + (3 if diffusion else 0)
-        return 1 + (1 if chemistry else 0) + per_box * (1 + len(self.shells)) + 2 * len(self.ghost_boxes)
+    def launches_per_step(self, diffusion, chemistry, scheme="Hybrid"):
+        from .core import rhs_launches
+        return rhs_launches(scheme, diffusion, chemistry) * (1 + len(self.shells)) + 2 * len(self.ghost_boxes)

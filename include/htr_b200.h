@@ -64,6 +64,10 @@ const char *htr_mixture_name(void);
 int  htr_sizeof_mix(void);        /* == sizeof(reference struct Mix) for this mixture */
 const char *htr_build_info(void); /* arch, flags */
 
+/* Library switches.  "fast" (default 1): htr_rhs uses the shared-memory staged kernels for the Hybrid and
+ * SkewSymmetric schemes; 0 = issue the per-task kernels only (same results; A/B testing). */
+int  htr_set_option(const char *name, int value);
+
 /* ---- mixture (replaces Mix::Mix(const Config&) + LoadMixtureTask) ----
  * The constructors fill `mix_out` (htr_sizeof_mix() bytes) with a POD that is byte-identical
  * to the reference's struct Mix, so an adapter may instead pass args.mix straight to
