@@ -60,7 +60,7 @@ def ncomp(c, nspec):
 def rhs_launches(scheme, diffusion, chemistry, fast=True):
     """Kernels one htr_rhs call launches (csrc/htr_kernels.cu: htr_rhs)."""
     if fast and scheme in ("Hybrid", "SkewSymmetric"):
-        return 2 + 3 + (3 if diffusion else 0)       # z+chem, xy, three masked generic passes, diffusion
+        return 5 + (5 if diffusion else 0)       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked
     return 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
 
 

@@ -111,7 +111,7 @@ constexpr size_t ZT_SMEM = sizeof(double)*NV*ZT_NC + ZT_NC + ZT_NT;
 
 template<bool HYBRID, bool CHEM>
 __global__ void __launch_bounds__(ZT_NT)
-euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask) {
+euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    extern __shared__ double smem[];
    double *s = smem;
    uint8_t *sSens = reinterpret_cast<uint8_t*>(smem + NV*ZT_NC);
@@ -182,6 +182,7 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
       HTR_UNROLL
       for (int e = 0; e < nEq; e++) Ct[e] = base[e];
       mask[maskIndex(c, tile)] = deferred;
+      if (deferred) *flag = 1;          // all writers store the same value
    }
 }
 
@@ -196,7 +197,7 @@ template<int TY> struct XYTile {
 
 template<int TY, bool HYBRID>
 __global__ void __launch_bounds__(32*TY)
-euler_xy_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask) {
+euler_xy_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    using T = XYTile<TY>;
    constexpr int W = T::W, NC = T::NC, NT = T::NT;
    extern __shared__ double smem[];
@@ -279,7 +280,247 @@ euler_xy_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_
          }
       }
       mask[maskIndex(c, tile)] = deferred;
+      if (deferred) *flag = 1;          // all writers store the same value
    }
+}
+
+} // namespace fast
+} // namespace htr
+
+// =============================================================================================
+// Diffusion flux, staged:   diffusion_staged_kernel<2,TJ>  Conserved_t += Dz
+//                           diffusion_staged_kernel<1,TJ>  Conserved_t += Dy; += Dx
+// (reference order z, y, x: src/prometeo.rg:560-578; arithmetic of src/prometeo_rhs.inl:1058-1215 with the
+// Std_node rows of Interp/Grad as constant-bank operands).
+//
+// Every cell of the (x, J) tile (J = y or z) plus one more column/row on the plus side is staged once:
+// its 2-point-stencil operands (rho, mu, lam, T, MixW(Xi), u, Xi, Di, rho*Yi) and the cell-centred
+// velocity derivatives the faces interpolate (the reference recomputes them per face: 4 getDeriv
+// triples per face, 12 per cell; here 7 resp. 4 scalars per staged cell).  A face is then ~60 shared
+// loads and the per-face species enthalpies.  Face exchange / deferral as in the Euler kernels.
+// =============================================================================================
+#include "htr_diffusion.cuh"
+
+namespace htr {
+namespace fast {
+
+template<int JD> struct DLay {
+   static constexpr bool DOX = (JD == 1);
+   static constexpr int NG = DOX ? 7 : 4;
+   static constexpr int O_RHO = 0, O_MU = 1, O_LAM = 2, O_T = 3, O_MW = 4, O_U = 5, O_X = 8, O_DI = 8 + nSpec,
+                        O_RY = 8 + 2*nSpec, O_G = 8 + 3*nSpec, NVD = O_G + NG;
+};
+
+HTR_DEV double derivStd(double xm1, double x, double xp1, double m) {
+   return (c_Grad[Std_node][0]*(x - xm1) + c_Grad[Std_node][1]*(xp1 - x))*m;
+}
+HTR_DEV double interpStd(double x1, double x2) { return c_Interp[Std_node][0]*x1 + c_Interp[Std_node][1]*x2; }
+
+// Stages cell q (already wrapped) into slot idx; returns true if a node type the fast path does not handle
+// is involved.  JD = 1: derivatives G0..G6 = dUdX dVdX dUdY dVdY dUdZ dVdZ dWdZ;  JD = 2: dUdX dWdX dVdY dWdY.
+template<int JD, int NC>
+HTR_DEV bool stageDiffCell(double *s, const int idx, const htr_fluid &f, const Pt &q, const htr_rect &B) {
+   using L = DLay<JD>;
+   s[L::O_RHO*NC + idx] = ld<double>(f.rho, q);
+   s[L::O_MU*NC + idx] = ld<double>(f.mu, q);
+   s[L::O_LAM*NC + idx] = ld<double>(f.lam, q);
+   s[L::O_T*NC + idx] = ld<double>(f.temperature, q);
+   double Xi[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      Xi[i] = ldc<double>(f.MolarFracs, q, i);
+      s[(L::O_X + i)*NC + idx] = Xi[i];
+      s[(L::O_DI + i)*NC + idx] = ldc<double>(f.Di, q, i);
+      s[(L::O_RY + i)*NC + idx] = ldc<double>(f.Conserved, q, i);
+   }
+   s[L::O_MW*NC + idx] = mix::GetMolarWeightFromXi(Xi);
+   double u[3];
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) { u[i] = ldc<double>(f.velocity, q, i); s[(L::O_U + i)*NC + idx] = u[i]; }
+
+   bool bad = false;
+   {  // d/dx
+      Pt a = q, b = q;
+      a.x = wrapCoord(q.x - 1, B.lo[0], B.hi[0]); b.x = wrapCoord(q.x + 1, B.lo[0], B.hi[0]);
+      bad = bad || (ld<int>(f.nType_x, q) != Std_node);
+      const double m = ld<double>(f.dcsi_d, q);
+      constexpr int c1 = (JD == 1) ? 1 : 2;       // second component needed: V (xy kernel) or W (z kernel)
+      s[(L::O_G + 0)*NC + idx] = derivStd(ldc<double>(f.velocity, a, 0), u[0], ldc<double>(f.velocity, b, 0), m);
+      s[(L::O_G + 1)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
+   }
+   {  // d/dy
+      Pt a = q, b = q;
+      a.y = wrapCoord(q.y - 1, B.lo[1], B.hi[1]); b.y = wrapCoord(q.y + 1, B.lo[1], B.hi[1]);
+      bad = bad || (ld<int>(f.nType_y, q) != Std_node);
+      const double m = ld<double>(f.deta_d, q);
+      constexpr int c0 = (JD == 1) ? 0 : 1, c1 = (JD == 1) ? 1 : 2;   // (U,V) or (V,W)
+      s[(L::O_G + 2)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c0), u[c0], ldc<double>(f.velocity, b, c0), m);
+      s[(L::O_G + 3)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
+   }
+   if (JD == 1) {  // d/dz
+      Pt a = q, b = q;
+      a.z = wrapCoord(q.z - 1, B.lo[2], B.hi[2]); b.z = wrapCoord(q.z + 1, B.lo[2], B.hi[2]);
+      bad = bad || (ld<int>(f.nType_z, q) != Std_node);
+      const double m = ld<double>(f.dzet_d, q);
+      HTR_UNROLL
+      for (int i = 0; i < 3; i++)
+         s[(L::O_G + 4 + i)*NC + idx] = derivStd(ldc<double>(f.velocity, a, i), u[i], ldc<double>(f.velocity, b, i), m);
+   }
+   return bad;
+}
+
+// Diffusion flux of the face between staged cells ip and iq = ip + 1 along `dir`; gA..gD are the staged
+// derivative slots in the order the stress formulas of `dir` use them:
+//   dir 0: dVdY dUdY dUdZ dWdZ    dir 1: dUdX dVdX dVdZ dWdZ    dir 2: dUdX dWdX dVdY dWdY
+template<int dir, int JD, int NC>
+HTR_DEV void diffFaceStd(double *Flux, const double *s, const int ip, const int iq, const double m_s,
+                         const int gA, const int gB, const int gC, const int gD) {
+   using L = DLay<JD>;
+   #define HTR_S(v, i) s[(v)*NC + (i)]
+   const double rho_s = interpStd(HTR_S(L::O_RHO, ip), HTR_S(L::O_RHO, iq));
+   const double iMixW_s = 1.0/interpStd(HTR_S(L::O_MW, ip), HTR_S(L::O_MW, iq));
+   const double Tp = HTR_S(L::O_T, ip), Tq = HTR_S(L::O_T, iq);
+   const double T_s = interpStd(Tp, Tq);
+   double heatFlux = interpStd(HTR_S(L::O_LAM, ip), HTR_S(L::O_LAM, iq))*m_s*(Tp - Tq);
+
+   double hi[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) hi[i] = mix::GetSpeciesEnthalpy(i, T_s);
+
+   double ViCorr = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      const double YiVi = interpStd(HTR_S(L::O_DI + i, ip), HTR_S(L::O_DI + i, iq))*
+                          m_s*(HTR_S(L::O_X + i, ip) - HTR_S(L::O_X + i, iq))*mix::GetSpeciesMolarWeight(i)*iMixW_s;
+      Flux[i] = -rho_s*YiVi;
+      heatFlux += rho_s*YiVi*hi[i];
+      ViCorr += YiVi;
+   }
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      const double rhoYiViCorr = interpStd(HTR_S(L::O_RY + i, ip), HTR_S(L::O_RY + i, iq))*ViCorr;
+      Flux[i] += rhoYiViCorr;
+      heatFlux -= rhoYiViCorr*hi[i];
+   }
+
+   double up[3], uq[3], dN[3];
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) { up[i] = HTR_S(L::O_U + i, ip); uq[i] = HTR_S(L::O_U + i, iq); dN[i] = m_s*(uq[i] - up[i]); }
+   const double mu_s = interpStd(HTR_S(L::O_MU, ip), HTR_S(L::O_MU, iq));
+   const double A = interpStd(HTR_S(L::O_G + gA, ip), HTR_S(L::O_G + gA, iq));
+   const double Bv = interpStd(HTR_S(L::O_G + gB, ip), HTR_S(L::O_G + gB, iq));
+   const double C = interpStd(HTR_S(L::O_G + gC, ip), HTR_S(L::O_G + gC, iq));
+   const double D = interpStd(HTR_S(L::O_G + gD, ip), HTR_S(L::O_G + gD, iq));
+   double sigma[3];
+   if (dir == 0) {
+      sigma[0] = mu_s*(4*dN[0] - 2*A - 2*D)/3;
+      sigma[1] = mu_s*(dN[1] + Bv);
+      sigma[2] = mu_s*(dN[2] + C);
+   } else if (dir == 1) {
+      sigma[0] = mu_s*(dN[0] + Bv);
+      sigma[1] = mu_s*(4*dN[1] - 2*A - 2*D)/3;
+      sigma[2] = mu_s*(dN[2] + C);
+   } else {
+      sigma[0] = mu_s*(dN[0] + Bv);
+      sigma[1] = mu_s*(dN[1] + D);
+      sigma[2] = mu_s*(4*dN[2] - 2*A - 2*C)/3;
+   }
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) Flux[irU + i] = sigma[i];
+   double uSigma = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) uSigma += interpStd(up[i], uq[i])*sigma[i];
+   Flux[irE] = (uSigma - heatFlux);
+   #undef HTR_S
+}
+
+template<int JD, int TJ> struct DTile {
+   static constexpr bool DOX = (JD == 1);
+   static constexpr int W = DOX ? 33 : 32, ROWS = TJ + 1, NC = W*ROWS, NT = 32*TJ;
+   static constexpr size_t SMEM = sizeof(double)*DLay<JD>::NVD*NC + NT;
+};
+
+template<int JD, int TJ>
+__global__ void __launch_bounds__(32*TJ)
+diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
+   using T = DTile<JD, TJ>;
+   using L = DLay<JD>;
+   constexpr bool DOX = T::DOX;
+   constexpr int W = T::W, NC = T::NC, NT = T::NT;
+   constexpr int KD = (JD == 1) ? 2 : 1;              // the direction the grid's third index runs along
+   extern __shared__ double smem[];
+   double *s = smem;
+   uint8_t *sFlag = reinterpret_cast<uint8_t*>(smem + L::NVD*NC);
+   static_assert(L::NVD*NC >= nEq*NT, "flux exchange reuses the staging buffer");
+
+   const int i = threadIdx.x, j = threadIdx.y;
+   const int tid = j*32 + i;
+   const int64_t cx0 = DOX ? (tile.lo[0] - 1 + (int64_t)blockIdx.x*31) : (tile.lo[0] + (int64_t)blockIdx.x*32);
+   const int64_t cJ0 = tile.lo[JD] - 1 + (int64_t)blockIdx.y*(TJ - 1);
+   const int64_t cK = tile.lo[KD] + blockIdx.z;
+   Pt c;
+   c.x = cx0 + i;
+   (JD == 1 ? c.y : c.z) = cJ0 + j;
+   (JD == 1 ? c.z : c.y) = cK;
+
+   bool bad = false;
+   for (int n = tid; n < NC; n += NT) {
+      const int rr = n/W, cc = n - rr*W;
+      const int64_t x = cx0 + cc, J = cJ0 + rr;
+      if (x <= tile.hi[0] + 1 && J <= tile.hi[JD] + 1) {
+         Pt q;
+         q.x = wrapCoord(x, B.lo[0], B.hi[0]);
+         (JD == 1 ? q.y : q.z) = wrapCoord(J, B.lo[JD], B.hi[JD]);
+         (JD == 1 ? q.z : q.y) = cK;
+         bad = stageDiffCell<JD, NC>(s, n, f, q, B) || bad;
+      }
+   }
+   const int64_t cJ = cJ0 + j;
+   const bool inTile = c.x <= tile.hi[0] && cJ <= tile.hi[JD];
+   const bool jAct = inTile && (!DOX || i >= 1), xAct = DOX && inTile && j >= 1;
+   Pt q = c;                                         // own cell, wrapped (it may be lo-1)
+   q.x = wrapCoord(c.x, B.lo[0], B.hi[0]);
+   (JD == 1 ? q.y : q.z) = wrapCoord(cJ, B.lo[JD], B.hi[JD]);
+   if (JD == 2 && jAct) bad = bad || (ld<int>(f.nType_z, q) != Std_node);
+   const bool anyBad = __syncthreads_or(bad);
+
+   const int own = j*W + i;
+   double FJ[nEq], Fx[nEq];
+   HTR_UNROLL
+   for (int e = 0; e < nEq; e++) { FJ[e] = 0.0; Fx[e] = 0.0; }
+   const bool ok = !anyBad;
+   if (ok && jAct) {
+      if (JD == 1) diffFaceStd<1, JD, NC>(FJ, s, own, own + W, ld<double>(f.deta_s, q), 0, 1, 5, 6);
+      else         diffFaceStd<2, JD, NC>(FJ, s, own, own + W, ld<double>(f.dzet_s, q), 0, 1, 2, 3);
+   }
+   if (DOX && ok && xAct) diffFaceStd<0, JD, NC>(Fx, s, own, own + 1, ld<double>(f.dcsi_s, q), 3, 2, 4, 6);
+   double Fm[nEq];
+   if (DOX) {
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) Fm[e] = __shfl_up_sync(0xffffffffu, Fx[e], 1);
+   }
+   __syncthreads();
+   double *sF = smem;
+   HTR_UNROLL
+   for (int e = 0; e < nEq; e++) sF[e*NT + tid] = FJ[e];
+   __syncthreads();
+   if (inTile && j >= 1 && (!DOX || i >= 1)) {
+      if (ok) {
+         double *Ct = at<double>(f.Conserved_t, c);
+         const double mJ = ld<double>(m_dOf<JD>(f), c);
+         const double mx = DOX ? ld<double>(f.dcsi_d, c) : 0.0;
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) {
+            double v = Ct[e];
+            v += mJ*(FJ[e] - sF[e*NT + tid - 32]);
+            if (DOX) v += mx*(Fx[e] - Fm[e]);
+            Ct[e] = v;
+         }
+      }
+      mask[maskIndex(c, tile)] = !ok;
+      if (!ok) *flag = 1;
+   }
+   (void)sFlag;
 }
 
 } // namespace fast

@@ -54,10 +54,9 @@ HTR_DEV void eulerFace(double *Flux, const htr_fluid &f, const Pt &p, int t, con
 // KIND = FLUX_EULER (SCHEME selects the reconstruction) or FLUX_DIFFUSION
 // MASKED: only the cells flagged in `mask` (dense over the tile, see htr_fast.cuh) are updated and only
 // the faces they need are evaluated; a block without flagged cells returns at once.
-template<int dir, int KIND, int SCHEME, bool MASKED = false>
-__global__ void __launch_bounds__(256)
-flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep,
-                       const uint8_t *__restrict__ mask = nullptr) {
+template<int dir, int KIND, int SCHEME, bool MASKED>
+HTR_DEV void fluxBlock(const unsigned bx, const unsigned by, const unsigned bz, const htr_fluid &f, const htr_rect &tile,
+                       const htr_rect &B, const EulerParams &ep, const uint8_t *__restrict__ mask) {
    using FB = FaceBlock<dir>;
    constexpr int NT = FB::X*FB::Y*FB::Z;
    __shared__ double sF[nEq][NT];
@@ -67,9 +66,9 @@ flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B,
    constexpr int CX = FB::X - (dir == 0), CY = FB::Y - (dir == 1), CZ = FB::Z - (dir == 2); // cells per block
    // cell on the minus side of this thread's face; fd == 0 is the face below the block's first cell
    Pt c;
-   c.x = tile.lo[0] + (int64_t)blockIdx.x*CX + threadIdx.x - (dir == 0);
-   c.y = tile.lo[1] + (int64_t)blockIdx.y*CY + threadIdx.y - (dir == 1);
-   c.z = tile.lo[2] + (int64_t)blockIdx.z*CZ + threadIdx.z - (dir == 2);
+   c.x = tile.lo[0] + (int64_t)bx*CX + threadIdx.x - (dir == 0);
+   c.y = tile.lo[1] + (int64_t)by*CY + threadIdx.y - (dir == 1);
+   c.z = tile.lo[2] + (int64_t)bz*CZ + threadIdx.z - (dir == 2);
    const bool inCross = (dir == 0 || c.x <= tile.hi[0]) && (dir == 1 || c.y <= tile.hi[1]) && (dir == 2 || c.z <= tile.hi[2]);
    const int64_t cd = (dir == 0) ? c.x : ((dir == 1) ? c.y : c.z);
    const bool active = inCross && (cd <= tile.hi[dir]);
@@ -115,6 +114,27 @@ flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B,
 }
 
 template<int dir, int KIND, int SCHEME>
+__global__ void __launch_bounds__(256)
+flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep) {
+   fluxBlock<dir, KIND, SCHEME, false>(blockIdx.x, blockIdx.y, blockIdx.z, f, tile, B, ep, nullptr);
+}
+
+// Generic flux pass over the cells the staged kernels deferred.  Persistent grid: nothing to do (the usual
+// case of a smooth periodic box) costs one flag load per CTA; otherwise the CTAs stride over the blocks of the
+// tile and skip those without flagged cells.
+template<int dir, int KIND, int SCHEME>
+__global__ void __launch_bounds__(256)
+masked_flux_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep,
+                    const uint8_t *__restrict__ mask, const int *__restrict__ flag, const unsigned gx, const unsigned gy, const unsigned gz) {
+   if (*flag == 0) return;
+   const unsigned total = gx*gy*gz;
+   for (unsigned vb = blockIdx.x; vb < total; vb += gridDim.x) {
+      fluxBlock<dir, KIND, SCHEME, true>(vb % gx, (vb/gx) % gy, vb/(gx*gy), f, tile, B, ep, mask);
+      __syncthreads();
+   }
+}
+
+template<int dir, int KIND, int SCHEME>
 static cudaError_t launchFlux(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep, cudaStream_t st) {
    using FB = FaceBlock<dir>;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
@@ -126,15 +146,23 @@ static cudaError_t launchFlux(const htr_fluid &f, const htr_rect &tile, const ht
    return cudaGetLastError();
 }
 
-template<int dir, int SCHEME>
-static cudaError_t launchEulerMasked(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
-                                     const uint8_t *mask, cudaStream_t st) {
+static int g_num_sms = 0;
+
+template<int dir, int KIND, int SCHEME>
+static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
+                                     const uint8_t *mask, const int *flag, cudaStream_t st) {
    using FB = FaceBlock<dir>;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
    const int C[3] = {FB::X - (dir == 0), FB::Y - (dir == 1), FB::Z - (dir == 2)};
-   dim3 grid((unsigned)((n[0] + C[0] - 1)/C[0]), (unsigned)((n[1] + C[1] - 1)/C[1]), (unsigned)((n[2] + C[2] - 1)/C[2]));
+   const unsigned gx = (unsigned)((n[0] + C[0] - 1)/C[0]), gy = (unsigned)((n[1] + C[1] - 1)/C[1]), gz = (unsigned)((n[2] + C[2] - 1)/C[2]);
+   if (g_num_sms == 0) {
+      int dev = 0; cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_num_sms <= 0) g_num_sms = 148;
+   }
+   const uint64_t total = (uint64_t)gx*gy*gz;
+   const unsigned grid = (unsigned)(total < (uint64_t)g_num_sms ? total : (uint64_t)g_num_sms);
    dim3 block(FB::X, FB::Y, FB::Z);
-   flux_divergence_kernel<dir, FLUX_EULER, SCHEME, true><<<grid, block, 0, st>>>(f, tile, B, ep, mask);
+   masked_flux_kernel<dir, KIND, SCHEME><<<grid, block, 0, st>>>(f, tile, B, ep, mask, flag, gx, gy, gz);
    return cudaGetLastError();
 }
 
@@ -147,7 +175,9 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    constexpr bool HY = (SCHEME == HTR_SCHEME_HYBRID);
    constexpr int TY = 8;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
-   uint8_t *maskZ = scratch, *maskXY = scratch + n[0]*n[1]*n[2];
+   int *flags = reinterpret_cast<int*>(scratch);      // cells deferred by: [0] Euler z, [1] Euler xy, [2] diffusion z, [3] diffusion xy
+   uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
+   { cudaError_t e = cudaMemsetAsync(flags, 0, 16, st); if (e != cudaSuccess) return e; }
    static bool attr = false;
    if (!attr) {
       cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
@@ -158,20 +188,51 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    {
       dim3 grid((unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1], (unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)));
       dim3 block(fast::ZT_X, fast::ZT_Z, 1);
-      if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ);
-      else      fast::euler_z_chem_kernel<HY, false><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ);
+      if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
+      else      fast::euler_z_chem_kernel<HY, false><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
-      if ((e = launchEulerMasked<2, SCHEME>(f, tile, B, ep, maskZ, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<2, FLUX_EULER, SCHEME>(f, tile, B, ep, maskZ, flags, st)) != cudaSuccess) return e;
    }
    {
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TY - 2)/(TY - 1)), (unsigned)n[2]);
       dim3 block(32, TY, 1);
-      fast::euler_xy_kernel<TY, HY><<<grid, block, fast::XYTile<TY>::SMEM, st>>>(f, tile, B, maskXY);
+      fast::euler_xy_kernel<TY, HY><<<grid, block, fast::XYTile<TY>::SMEM, st>>>(f, tile, B, maskXY, flags + 1);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
-      if ((e = launchEulerMasked<1, SCHEME>(f, tile, B, ep, maskXY, st)) != cudaSuccess) return e;
-      if ((e = launchEulerMasked<0, SCHEME>(f, tile, B, ep, maskXY, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
+   }
+   return cudaSuccess;
+}
+
+// Conserved_t += diffusion z; += y; += x through the staged kernels + masked generic passes (same scratch,
+// after launchFastEuler has consumed it in stream order; flags [2], [3] were cleared there).
+static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, uint8_t *scratch, cudaStream_t st) {
+   constexpr int TJ = 8;
+   const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
+   int *flags = reinterpret_cast<int*>(scratch);
+   uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
+   const EulerParams ep = {0, 0, 0};
+   static bool attr = false;
+   if (!attr) {
+      cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
+      cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
+      attr = true;
+   }
+   cudaError_t e;
+   {
+      dim3 grid((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
+      fast::diffusion_staged_kernel<2, TJ><<<grid, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(f, tile, B, maskZ, flags + 2);
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
+   }
+   {
+      dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
+      fast::diffusion_staged_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(f, tile, B, maskXY, flags + 3);
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
    }
    return cudaSuccess;
 }
@@ -563,18 +624,15 @@ int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const 
    if (scheme < 0 || scheme > HTR_SCHEME_SKEWSYMMETRIC) return HTR_EINVAL;
    if ((scheme == HTR_SCHEME_HYBRID || scheme == HTR_SCHEME_SKEWSYMMETRIC) && !g_no_fast) {
       const int64_t cells = (tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
-      uint8_t *scratch = (uint8_t*)scratchFor((size_t)(2*cells), st);
+      uint8_t *scratch = (uint8_t*)scratchFor((size_t)(2*cells + 16), st);
       if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
       const EulerParams ep = {RK0, RK1, deltaTime};
       cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
          ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st)
          : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st);
       if (e != cudaSuccess) return cuerr(e);
-      int rc = HTR_OK;
-      if (diffusion)
-         for (int d = 2; d >= 0; d--)
-            if ((rc = htr_diffusion_flux(d, f, tile, bounds, stream)) != HTR_OK) return rc;
-      return rc;
+      if (diffusion && (e = launchFastDiffusion(*f, *tile, *bounds, scratch, st)) != cudaSuccess) return cuerr(e);
+      return HTR_OK;
    }
    {  // Conserved_t = 0 over the tile (RK.InitializeTimeDerivatives, src/prometeo_rk.rg:61-87)
       zero_rhs_kernel<<<blocksFor(*tile, 128), 128, 0, st>>>(*f, *tile);

@@ -334,6 +334,106 @@ HTR_DEV void scatter(const R &r, double rate, double *w) {
    for (int i = 0; i < r.Neducts; i++) w[r.educts[i].ind] -= r.educts[i].nu*rate;
    for (int i = 0; i < r.Npducts; i++) w[r.pducts[i].ind] += r.pducts[i].nu*rate;
 }
+#ifndef HTR_EXACT_POW
+// ---- production kinetics: same rate laws, register-only evaluation -------------------------------
+// Differences from the operation-for-operation form below (kept for the strict build):
+//   * T^n e^{-E/T} (and the equilibrium factor of the backward rate) is ONE exp of the summed
+//     exponent, with log T evaluated once per cell -- no pow(); the result differs from
+//     pow()*exp()*exp() by the rounding of the exponent sum (<= ~2e-14 relative, tolerance 1e-10);
+//   * species indices taken from the reaction tables select registers by compare/select chains
+//     instead of indexing arrays in local memory; trip counts are the compile-time maxima, predicated.
+HTR_DEV double pick(const double *v, int ind) {
+   double r = v[0];
+   HTR_UNROLL
+   for (int s = 1; s < nSpec; s++) r = (ind == s) ? v[s] : r;
+   return r;
+}
+HTR_DEV double massActionFast(const StoichTerm *t, int n, int nmax, const double *C) {
+   double a = 1.0;
+   HTR_UNROLL
+   for (int i = 0; i < HTR_MAX_REACTANTS + HTR_MAX_PRODUCTS; i++) {
+      if (i < nmax && i < n) {
+         const double c = pick(C, t[i].ind);
+         a *= (t[i].nu == 1) ? c : pow(c, (double)t[i].nu);
+      }
+   }
+   return a;
+}
+template<class R>
+HTR_DEV double netRateFast(const R &r, double logT, double iT, double logTRP, const double *C, const double *G) {
+   double ex = 0.0;
+   if (r.k.n != 0.0) ex += r.k.n*logT;
+   if (fabs(r.k.EovR) > 1e-5) ex -= r.k.EovR*iT;
+   const double a = massActionFast(r.educts, r.Neducts, HTR_MAX_REACTANTS, C);
+   double rate = r.k.A*exp(ex)*a;
+   if (r.has_backward) {
+      double sumNu = 0.0, sumNuG = 0.0;
+      HTR_UNROLL
+      for (int i = 0; i < HTR_MAX_REACTANTS; i++)
+         if (i < r.Neducts) { sumNu -= r.educts[i].nu; sumNuG -= r.educts[i].nu*pick(G, r.educts[i].ind); }
+      HTR_UNROLL
+      for (int i = 0; i < HTR_MAX_PRODUCTS; i++)
+         if (i < r.Npducts) { sumNu += r.pducts[i].nu; sumNuG += r.pducts[i].nu*pick(G, r.pducts[i].ind); }
+      const double b = massActionFast(r.pducts, r.Npducts, HTR_MAX_PRODUCTS, C);
+      rate -= r.k.A*exp(ex + sumNuG + sumNu*logTRP)*b;
+   }
+   return rate;
+}
+template<class R>
+HTR_DEV void scatterFast(const R &r, double rate, double *w) {
+   HTR_UNROLL
+   for (int i = 0; i < HTR_MAX_REACTANTS; i++)
+      if (i < r.Neducts) {
+         const double d = r.educts[i].nu*rate;
+         HTR_UNROLL
+         for (int s = 0; s < nSpec; s++) if (r.educts[i].ind == s) w[s] -= d;
+      }
+   HTR_UNROLL
+   for (int i = 0; i < HTR_MAX_PRODUCTS; i++)
+      if (i < r.Npducts) {
+         const double d = r.pducts[i].nu*rate;
+         HTR_UNROLL
+         for (int s = 0; s < nSpec; s++) if (r.pducts[i].ind == s) w[s] += d;
+      }
+}
+HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, const double *Yi) {
+   const double T = Tn*c_mix.TRef;
+   const double P = Pn*c_mix.PRef;
+   const double rho = rhon*c_mix.rhoRef;
+   const double logT = log(T), iT = 1.0/T;
+   const double logTRP = logT + log(RGAS/P);
+   double G[nSpec], C[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      w[i] = 0.0;
+      C[i] = Yi[i]*rho/c_mix.species[i].W;
+      const double *c = spec::range(c_mix.species[i], T);
+      const double g = -0.5*c[0]*iT*iT + c[1]*iT*(1.0 + logT) + c[2]*(1.0 - logT) + c[7]*iT - c[8];
+      G[i] = g - 0.5*T*(c[3] + T*(c[4]/3 + T*(c[5]/6 + 0.1*T*c[6])));
+   }
+#if HTR_NREAC > 0
+   HTR_UNROLL
+   for (int r = 0; r < HTR_NREAC; r++)
+      scatterFast(c_mix.reactions[r], netRateFast(c_mix.reactions[r], logT, iT, logTRP, C, G), w);
+#endif
+#if HTR_NTBREAC > 0
+   HTR_UNROLL
+   for (int r = 0; r < HTR_NTBREAC; r++) {
+      const CollisionReaction &R = c_mix.tbReactions[r];
+      double c = 1.0;
+      if (R.Nthirdb > 0) {
+         c = P/(RGAS*T);
+         HTR_UNROLL
+         for (int i = 0; i < HTR_MAX_TB; i++)
+            if (i < R.Nthirdb) c += pick(C, R.thirdb[i].ind)*(R.thirdb[i].nu - 1.0);
+      }
+      scatterFast(R, c*netRateFast(R, logT, iT, logTRP, C, G), w);
+   }
+#endif
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) w[i] *= c_mix.species[i].W*c_mix.iwiRef;
+}
+#else
 // w_i in computational units from non-dimensional rho, P, T and mass fractions
 HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, const double *Yi) {
    const double T = Tn*c_mix.TRef;
@@ -366,6 +466,7 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) w[i] *= c_mix.species[i].W*c_mix.iwiRef;
 }
+#endif // HTR_EXACT_POW
 } // namespace mix
 #endif // HTR_MULTICOMP
 
