@@ -197,7 +197,7 @@ def run_gpu(args, rank, world, local_rank):
     cfg = getattr(synthetic, cfgname)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    solver = htr.Solver(cfg)
+    solver = htr.Solver(cfg, variant=args.variant)
     nspec, neq = solver.nspec, solver.neq
     tiles = tiles_for(world)
     gN = (n * tiles[0], n * tiles[1], n * tiles[2])
@@ -373,6 +373,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--variant", default="", help="library build variant (tuning experiments; default = production)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -18,6 +18,10 @@ FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-shared", "--
 # comparable with the reference's CPU tasks; used by the parity tests to separate rounding
 # from logic.
 VARIANTS = {"": [], "strict": ["-fmad=false", "-DHTR_EXACT_POW", "-DHTR_FMAD_OFF"]}
+# tuning experiments: HTR_EXP="name1:-DA=1,-DB=2;name2:-DC=3" adds variants built on request (--variants name1 name2)
+for _e in filter(None, os.environ.get("HTR_EXP", "").split(";")):
+    _n, _f = _e.split(":", 1)
+    VARIANTS[_n] = [x for x in _f.split(",") if x]
 
 
 def lib_path(mix, variant=""):

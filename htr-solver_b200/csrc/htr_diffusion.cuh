@@ -44,8 +44,7 @@ HTR_DEV void diffusionFaceFlux(double *Flux, const htr_fluid &f, const Pt &p, co
    double heatFlux = Interp2Staggered(t, ld<double>(f.lam, p), ld<double>(f.lam, pp1))*m_s*(Tp - Tq);
 
    double hi[nSpec];
-   HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) hi[i] = mix::GetSpeciesEnthalpy(i, T_s);
+   mix::GetSpeciesEnthalpies(hi, T_s);
 
    double ViCorr = 0.0;
    HTR_UNROLL

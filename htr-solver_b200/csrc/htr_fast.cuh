@@ -28,6 +28,17 @@
 #pragma once
 #include "htr_euler.cuh"
 
+// resident CTAs per SM the register allocation aims at (tuned on B200 with ncu, see profiles/)
+#ifndef HTR_K1_MINB
+#define HTR_K1_MINB 2
+#endif
+#ifndef HTR_K2_MINB
+#define HTR_K2_MINB 2
+#endif
+#ifndef HTR_D_MINB
+#define HTR_D_MINB 3
+#endif
+
 namespace htr {
 namespace fast {
 
@@ -110,7 +121,7 @@ constexpr int ZT_X = 32, ZT_Z = 16, ZT_ROWS = ZT_Z + 5, ZT_NC = ZT_ROWS*ZT_X, ZT
 constexpr size_t ZT_SMEM = sizeof(double)*NV*ZT_NC + ZT_NC + ZT_NT;
 
 template<bool HYBRID, bool CHEM>
-__global__ void __launch_bounds__(ZT_NT)
+__global__ void __launch_bounds__(ZT_NT, HTR_K1_MINB)
 euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    extern __shared__ double smem[];
    double *s = smem;
@@ -196,7 +207,7 @@ template<int TY> struct XYTile {
 };
 
 template<int TY, bool HYBRID>
-__global__ void __launch_bounds__(32*TY)
+__global__ void __launch_bounds__(32*TY, HTR_K2_MINB)
 euler_xy_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    using T = XYTile<TY>;
    constexpr int W = T::W, NC = T::NC, NT = T::NT;
@@ -384,8 +395,7 @@ HTR_DEV void diffFaceStd(double *Flux, const double *s, const int ip, const int 
    double heatFlux = interpStd(HTR_S(L::O_LAM, ip), HTR_S(L::O_LAM, iq))*m_s*(Tp - Tq);
 
    double hi[nSpec];
-   HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) hi[i] = mix::GetSpeciesEnthalpy(i, T_s);
+   mix::GetSpeciesEnthalpies(hi, T_s);
 
    double ViCorr = 0.0;
    HTR_UNROLL
@@ -441,7 +451,7 @@ template<int JD, int TJ> struct DTile {
 };
 
 template<int JD, int TJ>
-__global__ void __launch_bounds__(32*TJ)
+__global__ void __launch_bounds__(32*TJ, HTR_D_MINB)
 diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    using T = DTile<JD, TJ>;
    using L = DLay<JD>;

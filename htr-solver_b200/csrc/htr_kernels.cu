@@ -515,6 +515,23 @@ int htr_set_option(const char *name, int value) {
 int htr_set_mixture(const void *mix, size_t bytes) {
    if (!mix || bytes != sizeof(MixData)) return HTR_EINVAL;
    cudaError_t e = cudaMemcpyToSymbol(c_mix, mix, sizeof(MixData));
+#if HTR_MULTICOMP
+   if (e == cudaSuccess) {
+      MixData m;
+      memcpy(&m, mix, sizeof(m));
+      SpecDerived der[nSpec];
+      for (int i = 0; i < nSpec; i++) {
+         der[i].rOvW = RGAS/m.species[i].W;
+         const double *cp[3] = {m.species[i].cp.cpH, m.species[i].cp.cpM, m.species[i].cp.cpL};
+         for (int r = 0; r < 3; r++) {
+            const double *c = cp[r];
+            der[i].q[r][0] = c[3]*0.50; der[i].q[r][1] = c[4]/3; der[i].q[r][2] = c[5]*0.25;
+            der[i].q[r][3] = c[6]/5;    der[i].q[r][4] = c[5]/6;
+         }
+      }
+      e = cudaMemcpyToSymbol(c_der, der, sizeof(der));
+   }
+#endif
    if (e == cudaSuccess) g_mix_loaded = true;
    return cuerr(e);
 }

@@ -11,6 +11,12 @@
 namespace htr {
 
 __constant__ MixData c_mix;
+#if HTR_MULTICOMP
+// Quotients of table constants, evaluated once on the host with the reference's own expressions
+// (src/Mixtures/Species.inl: RGAS/W, cp[3]*0.50, cp[4]/3, cp[5]*0.25, cp[6]/5, cp[5]/6) for the ranges H, M, L.
+struct SpecDerived { double rOvW; double q[3][5]; };
+__constant__ SpecDerived c_der[HTR_NSPEC];
+#endif
 
 #define HTR_DEV __device__ __forceinline__
 #define HTR_UNROLL _Pragma("unroll")
@@ -30,6 +36,7 @@ HTR_DEV void   GetYi(double *Yi, double rho, const double *rhoYi) { Yi[0] = rhoY
 HTR_DEV double GetRho(double P, double T, double MixW) { return P/(c_mix.R*T); }
 HTR_DEV double GetHeatCapacity(double T, const double *Yi) { return c_mix.gamma/(c_mix.gamma - 1)*c_mix.R; }
 HTR_DEV double GetSpeciesEnthalpy(int i, double T) { return c_mix.gamma/(c_mix.gamma - 1)*c_mix.R*T; }
+HTR_DEV void   GetSpeciesEnthalpies(double *hi, double T) { hi[0] = c_mix.gamma/(c_mix.gamma - 1)*c_mix.R*T; }
 HTR_DEV double GetSpeciesMolarWeight(int i) { return RGAS/c_mix.R; }
 HTR_DEV double GetInternalEnergy(double T, const double *Yi) { return T*c_mix.R/(c_mix.gamma - 1.0); }
 HTR_DEV double GetTFromInternalEnergy(double e0, double T, const double *Yi) { return e0*(c_mix.gamma - 1.0)/c_mix.R; }
@@ -58,30 +65,34 @@ HTR_DEV void   Getdpdrhoi(double *dpdrhoi, double gamma, double T, const double 
 // Multi-component ideal-gas mixture with NASA-9 thermodynamics
 // ------------------------------------------------------------------------------------------
 namespace spec {
-// polynomial range for temperature T (dimensional); switch temperatures are floats promoted to double
-HTR_DEV const double *range(const SpeciesData &s, double T) {
-   return (T > s.cp.TSwitch2) ? s.cp.cpH : ((T > s.cp.TSwitch1) ? s.cp.cpM : s.cp.cpL);
+// polynomial range for temperature T (dimensional); switch temperatures are floats promoted to double:
+// 0 = high (cpH), 1 = middle (cpM), 2 = low (cpL), which are contiguous in NasaPoly
+HTR_DEV int rangeIndex(const SpeciesData &s, double T) {
+   return (T > s.cp.TSwitch2) ? 0 : ((T > s.cp.TSwitch1) ? 1 : 2);
 }
-HTR_DEV double GetCp(const SpeciesData &s, double T) {
-   const double rOvW = RGAS/s.W;
-   const double Tinv = 1.0/T;
+HTR_DEV const double *range(const SpeciesData &s, double T) { return s.cp.cpH + 9*rangeIndex(s, T); }
+// The quotients of table constants that the reference evaluates per call (RGAS/W, c4/3, c6/5, c5/6) come from
+// c_der: the same IEEE divisions done once on the host (htr_set_mixture), hence the same bits.  log T and 1/T
+// are taken once per temperature by the callers (same bits as taking them per species).
+HTR_DEV double GetCp(const SpeciesData &s, const SpecDerived &d, double T, double Tinv) {
    const double *c = range(s, T);
-   return rOvW*(c[0]*Tinv*Tinv + c[1]*Tinv + c[2] + T*(c[3] + T*(c[4] + T*(c[5] + T*c[6]))));
+   return d.rOvW*(c[0]*Tinv*Tinv + c[1]*Tinv + c[2] + T*(c[3] + T*(c[4] + T*(c[5] + T*c[6]))));
 }
-HTR_DEV double GetEnthalpy(const SpeciesData &s, double T) {
-   const double rOvW = RGAS/s.W;
-   const double Tinv = 1.0/T;
-   const double *c = range(s, T);
-   const double E = -c[0]*Tinv + c[1]*log(T) + c[7] + T*(c[2] + T*(c[3]*0.50 + T*(c[4]/3 + T*(c[5]*0.25 + c[6]/5*T))));
-   return E*rOvW;
+HTR_DEV double GetEnthalpy(const SpeciesData &s, const SpecDerived &d, double T, double Tinv, double logT) {
+   const int r = rangeIndex(s, T);
+   const double *c = s.cp.cpH + 9*r;
+   const double *q = d.q[r];
+   const double E = -c[0]*Tinv + c[1]*logT + c[7] + T*(c[2] + T*(q[0] + T*(q[1] + T*(q[2] + q[3]*T))));
+   return E*d.rOvW;
 }
-HTR_DEV double GetFreeEnthalpy(const SpeciesData &s, double T) {   // H/(RT) - S/R
-   const double Tinv = 1.0/T;
-   const double logT = log(T);
-   const double *c = range(s, T);
+HTR_DEV double GetFreeEnthalpy(const SpeciesData &s, const SpecDerived &d, double T, double Tinv, double logT) {   // H/(RT) - S/R
+   const int r = rangeIndex(s, T);
+   const double *c = s.cp.cpH + 9*r;
+   const double *q = d.q[r];
    const double G = -0.5*c[0]*Tinv*Tinv + c[1]*Tinv*(1.0 + logT) + c[2]*(1.0 - logT) + c[7]*Tinv - c[8];
-   return G - 0.5*T*(c[3] + T*(c[4]/3 + T*(c[5]/6 + 0.1*T*c[6])));
+   return G - 0.5*T*(c[3] + T*(q[1] + T*(q[4] + 0.1*T*c[6])));
 }
+HTR_DEV double GetCp(const SpeciesData &s, const SpecDerived &d, double T) { return GetCp(s, d, T, 1.0/T); }
 // reduced collision integrals, rational fits in T* = T kb/eps
 HTR_DEV double omega_mu(double T) {
    const double num = 3.3530622607 + T*(2.53272006 + T*(2.9024238575 + T*0.11186138893));
@@ -132,14 +143,14 @@ HTR_DEV double GetFZrot(const SpeciesData &s, double T) {
    return 1 + 0.5*pow(PI, 1.5)*sqrt(tmp) + (2 + 0.25*PI*PI)*tmp + pow(PI, 1.5)*pow(tmp, 1.5);
 }
 // Species conductivity: monatomic (Eucken 15/4) or modified-Eucken with rotational relaxation
-HTR_DEV double GetLam(const SpeciesData &s, double T) {
+HTR_DEV double GetLam(const SpeciesData &s, const SpecDerived &d, double T) {
    const double mu = GetMu(s, T);
    if (s.diff.Geom == 0) return 15.0/4*mu*RGAS/s.W;
    const bool lin = (s.diff.Geom == 1);
    const double CvROvR = lin ? 1.0 : 1.5;
    const double CvT = 1.5*RGAS;
    const double CvR = CvROvR*RGAS;
-   const double CvV = GetCp(s, T)*s.W - (lin ? 3.5 : 4.0)*RGAS;
+   const double CvV = GetCp(s, d, T)*s.W - (lin ? 3.5 : 4.0)*RGAS;
    const double Dkk = GetSelfDiffusion(s, T);
    const double fV = Dkk/mu;
    const double Zrot = s.diff.Z298*GetFZrot(s, 298.0)/GetFZrot(s, T);
@@ -190,18 +201,30 @@ HTR_DEV void GetYi(double *Yi, double rho, const double *rhoYi) {
 HTR_DEV double GetRho(double P, double T, double MixW) { return P*MixW*c_mix.iMixWRef/T; }
 HTR_DEV double GetHeatCapacity(double Tn, const double *Yi) {
    const double T = Tn*c_mix.TRef;
+   const double Tinv = 1.0/T;
    double cp = 0.0;
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) cp += Yi[i]*spec::GetCp(c_mix.species[i], T);
+   for (int i = 0; i < nSpec; i++) cp += Yi[i]*spec::GetCp(c_mix.species[i], c_der[i], T, Tinv);
    return cp*c_mix.iCpRef;
 }
-HTR_DEV double GetSpeciesEnthalpy(int i, double T) { return spec::GetEnthalpy(c_mix.species[i], T*c_mix.TRef)*c_mix.ieRef; }
+HTR_DEV double GetSpeciesEnthalpy(int i, double Tn) {
+   const double T = Tn*c_mix.TRef;
+   return spec::GetEnthalpy(c_mix.species[i], c_der[i], T, 1.0/T, log(T))*c_mix.ieRef;
+}
+// all species at one temperature: one log, one reciprocal
+HTR_DEV void GetSpeciesEnthalpies(double *hi, double Tn) {
+   const double T = Tn*c_mix.TRef;
+   const double Tinv = 1.0/T, logT = log(T);
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) hi[i] = spec::GetEnthalpy(c_mix.species[i], c_der[i], T, Tinv, logT)*c_mix.ieRef;
+}
 HTR_DEV double GetSpeciesMolarWeight(int i) { return c_mix.species[i].W; }
 HTR_DEV double GetInternalEnergy(double Tn, const double *Yi) {
    const double T = Tn*c_mix.TRef;
+   const double Tinv = 1.0/T, logT = log(T);
    double e = 0.0;
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) e += Yi[i]*(spec::GetEnthalpy(c_mix.species[i], T) - RGAS*T/c_mix.species[i].W);
+   for (int i = 0; i < nSpec; i++) e += Yi[i]*(spec::GetEnthalpy(c_mix.species[i], c_der[i], T, Tinv, logT) - RGAS*T/c_mix.species[i].W);
    return e*c_mix.ieRef;
 }
 // Newton iteration on e(T) = e0 from the caller's guess (step tolerance 1e-8 on non-dimensional T)
@@ -211,9 +234,10 @@ HTR_DEV double GetTFromInternalEnergy(double e0, double T, const double *Yi) {
       const double f = e0 - GetInternalEnergy(T, Yi);
       if (fabs(f/dfdT) < 1e-8) break;
       dfdT = 0.0;
+      const double Td = T*c_mix.TRef, Tdinv = 1.0/Td;
       HTR_UNROLL
       for (int i = 0; i < nSpec; i++)
-         dfdT += Yi[i]*(spec::GetCp(c_mix.species[i], T*c_mix.TRef) - RGAS/c_mix.species[i].W)*c_mix.iCpRef;
+         dfdT += Yi[i]*(spec::GetCp(c_mix.species[i], c_der[i], Td, Tdinv) - c_der[i].rOvW)*c_mix.iCpRef;
       T += f/dfdT;
    }
    return T;
@@ -245,7 +269,7 @@ HTR_DEV double GetHeatConductivity(double Tn, const double *Xi) {
    double a = 0.0, b = 0.0;
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
-      const double lami = spec::GetLam(c_mix.species[i], T);
+      const double lami = spec::GetLam(c_mix.species[i], c_der[i], T);
       a += Xi[i]*lami;
       b += Xi[i]/lami;
    }
@@ -283,10 +307,11 @@ HTR_DEV void GetDiffusivity(double *Di, double Pn, double Tn, double MixW, const
 HTR_DEV double Getdpde(double rho, double gamma) { return rho*(gamma - 1); }
 HTR_DEV void Getdpdrhoi(double *dpdrhoi, double gamma, double Tn, const double *Yi) {
    const double T = Tn*c_mix.TRef;
+   const double Tinv = 1.0/T, logT = log(T);
    double e = 0.0;
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
-      dpdrhoi[i] = spec::GetEnthalpy(c_mix.species[i], T) - RGAS*T/c_mix.species[i].W;
+      dpdrhoi[i] = spec::GetEnthalpy(c_mix.species[i], c_der[i], T, Tinv, logT) - RGAS*T/c_mix.species[i].W;
       e += Yi[i]*dpdrhoi[i];
    }
    HTR_UNROLL
@@ -407,9 +432,7 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
    for (int i = 0; i < nSpec; i++) {
       w[i] = 0.0;
       C[i] = Yi[i]*rho/c_mix.species[i].W;
-      const double *c = spec::range(c_mix.species[i], T);
-      const double g = -0.5*c[0]*iT*iT + c[1]*iT*(1.0 + logT) + c[2]*(1.0 - logT) + c[7]*iT - c[8];
-      G[i] = g - 0.5*T*(c[3] + T*(c[4]/3 + T*(c[5]/6 + 0.1*T*c[6])));
+      G[i] = spec::GetFreeEnthalpy(c_mix.species[i], c_der[i], T, iT, logT);
    }
 #if HTR_NREAC > 0
    HTR_UNROLL
@@ -444,7 +467,7 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
    for (int i = 0; i < nSpec; i++) {
       w[i] = 0.0;
       C[i] = Yi[i]*rho/c_mix.species[i].W;
-      G[i] = spec::GetFreeEnthalpy(c_mix.species[i], T);
+      G[i] = spec::GetFreeEnthalpy(c_mix.species[i], c_der[i], T, 1.0/T, log(T));
    }
 #if HTR_NREAC > 0
    HTR_UNROLL
