@@ -199,6 +199,9 @@ def run_gpu(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     solver = htr.Solver(cfg, variant=args.variant)
     nspec, neq = solver.nspec, solver.neq
+    for kv in args.opt:                      # library switches for A/B runs, e.g. --opt bulk=0
+        k, v = kv.split("=")
+        solver.set_option(k, int(v))
     tiles = tiles_for(world)
     gN = (n * tiles[0], n * tiles[1], n * tiles[2])
     tc = (rank % tiles[0], (rank // tiles[0]) % tiles[1], rank // (tiles[0] * tiles[1]))
@@ -373,6 +376,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="htr_set_option name=value (A/B runs)")
     ap.add_argument("--variant", default="", help="library build variant (tuning experiments; default = production)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

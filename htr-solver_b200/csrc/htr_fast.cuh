@@ -147,10 +147,13 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
       }
    }
    const bool faceActive = inX && c.z <= tile.hi[2];
+   const bool upd = faceActive && k >= 1;
    bool bad = false;
+   double mz = 0.0, Tc = 0.0;
    if (faceActive) {
       const Pt q = {c.x, c.y, wrapCoord(c.z, B.lo[2], B.hi[2])};
       bad = ld<int>(f.nType_z, q) != Std_node;
+      if (upd) { mz = ld<double>(f.dzet_e, c); if (CHEM) Tc = ld<double>(f.temperature, c); }
    }
    const bool anyBad = __syncthreads_or(bad);
 
@@ -160,7 +163,6 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
       if (HYBRID) smooth = sSens[(k + 1)*ZT_X + i] && sSens[(k + 2)*ZT_X + i] && sSens[(k + 3)*ZT_X + i];
       if (smooth) kgStdFlux<2, ZT_NC>(F, s, k*ZT_X + i, ZT_X);
    }
-   const bool upd = faceActive && k >= 1;
    double base[nEq];
    HTR_UNROLL
    for (int e = 0; e < nEq; e++) base[e] = 0.0;
@@ -169,7 +171,7 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
       double Yi[nSpec], w[nSpec];
       HTR_UNROLL
       for (int e = 0; e < nSpec; e++) Yi[e] = s[(V_Y + e)*ZT_NC + own];
-      mix::GetProductionRates(w, s[V_RHO*ZT_NC + own], s[V_P*ZT_NC + own], ld<double>(f.temperature, c), Yi);
+      mix::GetProductionRates(w, s[V_RHO*ZT_NC + own], s[V_P*ZT_NC + own], Tc, Yi);
       HTR_UNROLL
       for (int e = 0; e < nSpec; e++) base[e] += w[e];
    }
@@ -185,9 +187,8 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
    if (upd) {
       const bool deferred = !(have && sFlag[tid - ZT_X]);
       if (!deferred) {
-         const double m = ld<double>(f.dzet_e, c);
          HTR_UNROLL
-         for (int e = 0; e < nEq; e++) base[e] += m*(F[e] - sF[e*ZT_NT + tid - ZT_X]);
+         for (int e = 0; e < nEq; e++) base[e] += mz*(F[e] - sF[e*ZT_NT + tid - ZT_X]);
       }
       double *Ct = at<double>(f.Conserved_t, c);
       HTR_UNROLL
@@ -473,6 +474,18 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    (JD == 1 ? c.y : c.z) = cJ0 + j;
    (JD == 1 ? c.z : c.y) = cK;
 
+   const int64_t cJ = cJ0 + j;
+   const bool inTile = c.x <= tile.hi[0] && cJ <= tile.hi[JD];
+   // own Conserved_t and metrics requested before the staging loop (latency hidden behind it)
+   const bool upd = inTile && j >= 1 && (!DOX || i >= 1);
+   double *Ct = at<double>(f.Conserved_t, c);
+   double ct[nEq], mJ = 0.0, mx = 0.0;
+   if (upd) {
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) ct[e] = Ct[e];
+      mJ = ld<double>(m_dOf<JD>(f), c);
+      if (DOX) mx = ld<double>(f.dcsi_d, c);
+   }
    bool bad = false;
    for (int n = tid; n < NC; n += NT) {
       const int rr = n/W, cc = n - rr*W;
@@ -485,8 +498,7 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
          bad = stageDiffCell<JD, NC>(s, n, f, q, B) || bad;
       }
    }
-   const int64_t cJ = cJ0 + j;
-   const bool inTile = c.x <= tile.hi[0] && cJ <= tile.hi[JD];
+
    const bool jAct = inTile && (!DOX || i >= 1), xAct = DOX && inTile && j >= 1;
    Pt q = c;                                         // own cell, wrapped (it may be lo-1)
    q.x = wrapCoord(c.x, B.lo[0], B.hi[0]);
@@ -514,14 +526,11 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    HTR_UNROLL
    for (int e = 0; e < nEq; e++) sF[e*NT + tid] = FJ[e];
    __syncthreads();
-   if (inTile && j >= 1 && (!DOX || i >= 1)) {
+   if (upd) {
       if (ok) {
-         double *Ct = at<double>(f.Conserved_t, c);
-         const double mJ = ld<double>(m_dOf<JD>(f), c);
-         const double mx = DOX ? ld<double>(f.dcsi_d, c) : 0.0;
          HTR_UNROLL
          for (int e = 0; e < nEq; e++) {
-            double v = Ct[e];
+            double v = ct[e];
             v += mJ*(FJ[e] - sF[e*NT + tid - 32]);
             if (DOX) v += mx*(Fx[e] - Fm[e]);
             Ct[e] = v;

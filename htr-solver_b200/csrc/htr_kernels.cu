@@ -11,10 +11,13 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <initializer_list>
+#include <utility>
 #include "htr_euler.cuh"
 #include "htr_diffusion.cuh"
 #include "htr_pointwise.cuh"
 #include "htr_fast.cuh"
+#include "htr_fast_bulk.cuh"
 
 namespace htr {
 
@@ -169,6 +172,22 @@ static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const 
 // Fast path of  Conserved_t = 0 (+chem) + Euler z,y,x  for the Hybrid and SkewSymmetric schemes
 // (htr_fast.cuh) followed by the masked generic kernels for the cells it deferred.
 // `scratch` holds two mask bytes per cell of the tile.
+static bool g_no_bulk = false;          // htr_set_option("bulk", 0): cooperative loads instead of TMA bulk copies
+
+// Can rows of these fields be moved by cp.async.bulk?  Returns 0 (no) or 1 | parity<<1 (htr_bulk.cuh).
+static int bulkEligible(std::initializer_list<std::pair<const htr_acc*, int>> fields) {
+   if (g_no_bulk) return 0;
+   int parity = -1;
+   for (auto &fc : fields) {
+      const htr_acc &a = *fc.first;
+      const uintptr_t b = (uintptr_t)a.base;
+      if (a.stride[0] != 8*fc.second || (a.stride[1] & 15) || (a.stride[2] & 15) || (b & 7)) return 0;
+      const int p = (int)((b >> 3) & 1);
+      if (parity < 0) parity = p; else if (p != parity) return 0;
+   }
+   return 1 | (parity << 1);
+}
+
 template<int SCHEME>
 static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
                                    const EulerParams &ep, uint8_t *scratch, cudaStream_t st) {
@@ -182,7 +201,7 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    if (!attr) {
       cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
       cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
-      cudaFuncSetAttribute(fast::euler_xy_kernel<TY, HY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::XYTile<TY>::SMEM);
+      cudaFuncSetAttribute(fast::euler_xy_bulk_kernel<TY, HY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::XYB<TY>::SMEM);
       attr = true;
    }
    {
@@ -197,7 +216,8 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    {
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TY - 2)/(TY - 1)), (unsigned)n[2]);
       dim3 block(32, TY, 1);
-      fast::euler_xy_kernel<TY, HY><<<grid, block, fast::XYTile<TY>::SMEM, st>>>(f, tile, B, maskXY, flags + 1);
+      const int bulkOK = bulkEligible({{&f.rho, 1}, {&f.pressure, 1}, {&f.velocity, 3}, {&f.MassFracs, nSpec}});
+      fast::euler_xy_bulk_kernel<TY, HY><<<grid, block, fast::XYB<TY>::SMEM, st>>>(f, tile, B, maskXY, flags + 1, bulkOK);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
@@ -509,11 +529,44 @@ int htr_mix_init_multicomp(void *out, double LRef, double PRef, double TRef,
 int htr_set_option(const char *name, int value) {
    if (!name) return HTR_EINVAL;
    if (strcmp(name, "fast") == 0) { g_no_fast = (value == 0); return HTR_OK; }
+   if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
    return HTR_EINVAL;
 }
 
 int htr_set_mixture(const void *mix, size_t bytes) {
    if (!mix || bytes != sizeof(MixData)) return HTR_EINVAL;
+#if HTR_MULTICOMP
+   // the production kinetics are specialised on the structure of this library's mechanism
+   // (compared field by field: padding bytes of a caller-constructed struct are not defined)
+   {
+      MixData a, b;
+      memcpy(&a, mix, sizeof(a));
+      memset(&b, 0, sizeof(b));
+      memcpy(&b, HTR_TABLES, HTR_TABLE_BYTES);
+      auto sameTerms = [](const StoichTerm *x, const StoichTerm *y, int n) {
+         for (int i = 0; i < n; i++) if (x[i].ind != y[i].ind || x[i].nu != y[i].nu) return false;
+         return true;
+      };
+      auto sameK = [](const Arrhenius &x, const Arrhenius &y) {
+         return (x.n != 0.0f) == (y.n != 0.0f) && (fabsf(x.EovR) > 1e-5f) == (fabsf(y.EovR) > 1e-5f);
+      };
+#if HTR_NREAC > 0
+      for (int r = 0; r < HTR_NREAC; r++) {
+         const PlainReaction &x = a.reactions[r], &y = b.reactions[r];
+         if (x.has_backward != y.has_backward || x.Neducts != y.Neducts || x.Npducts != y.Npducts || !sameK(x.k, y.k) ||
+             !sameTerms(x.educts, y.educts, y.Neducts) || !sameTerms(x.pducts, y.pducts, y.Npducts)) return HTR_EMIXTYPE;
+      }
+#endif
+#if HTR_NTBREAC > 0
+      for (int r = 0; r < HTR_NTBREAC; r++) {
+         const CollisionReaction &x = a.tbReactions[r], &y = b.tbReactions[r];
+         if (x.has_backward != y.has_backward || x.Neducts != y.Neducts || x.Npducts != y.Npducts || x.Nthirdb != y.Nthirdb ||
+             !sameK(x.k, y.k) || !sameTerms(x.educts, y.educts, y.Neducts) || !sameTerms(x.pducts, y.pducts, y.Npducts) ||
+             !sameTerms(x.thirdb, y.thirdb, y.Nthirdb)) return HTR_EMIXTYPE;
+      }
+#endif
+   }
+#endif
    cudaError_t e = cudaMemcpyToSymbol(c_mix, mix, sizeof(MixData));
 #if HTR_MULTICOMP
    if (e == cudaSuccess) {

@@ -365,63 +365,17 @@ HTR_DEV void scatter(const R &r, double rate, double *w) {
 //   * T^n e^{-E/T} (and the equilibrium factor of the backward rate) is ONE exp of the summed
 //     exponent, with log T evaluated once per cell -- no pow(); the result differs from
 //     pow()*exp()*exp() by the rounding of the exponent sum (<= ~2e-14 relative, tolerance 1e-10);
-//   * species indices taken from the reaction tables select registers by compare/select chains
-//     instead of indexing arrays in local memory; trip counts are the compile-time maxima, predicated.
-HTR_DEV double pick(const double *v, int ind) {
-   double r = v[0];
-   HTR_UNROLL
-   for (int s = 1; s < nSpec; s++) r = (ind == s) ? v[s] : r;
-   return r;
-}
-HTR_DEV double massActionFast(const StoichTerm *t, int n, int nmax, const double *C) {
-   double a = 1.0;
-   HTR_UNROLL
-   for (int i = 0; i < HTR_MAX_REACTANTS + HTR_MAX_PRODUCTS; i++) {
-      if (i < nmax && i < n) {
-         const double c = pick(C, t[i].ind);
-         a *= (t[i].nu == 1) ? c : pow(c, (double)t[i].nu);
-      }
-   }
-   return a;
-}
-template<class R>
-HTR_DEV double netRateFast(const R &r, double logT, double iT, double logTRP, const double *C, const double *G) {
-   double ex = 0.0;
-   if (r.k.n != 0.0) ex += r.k.n*logT;
-   if (fabs(r.k.EovR) > 1e-5) ex -= r.k.EovR*iT;
-   const double a = massActionFast(r.educts, r.Neducts, HTR_MAX_REACTANTS, C);
-   double rate = r.k.A*exp(ex)*a;
-   if (r.has_backward) {
-      double sumNu = 0.0, sumNuG = 0.0;
-      HTR_UNROLL
-      for (int i = 0; i < HTR_MAX_REACTANTS; i++)
-         if (i < r.Neducts) { sumNu -= r.educts[i].nu; sumNuG -= r.educts[i].nu*pick(G, r.educts[i].ind); }
-      HTR_UNROLL
-      for (int i = 0; i < HTR_MAX_PRODUCTS; i++)
-         if (i < r.Npducts) { sumNu += r.pducts[i].nu; sumNuG += r.pducts[i].nu*pick(G, r.pducts[i].ind); }
-      const double b = massActionFast(r.pducts, r.Npducts, HTR_MAX_PRODUCTS, C);
-      rate -= r.k.A*exp(ex + sumNuG + sumNu*logTRP)*b;
-   }
-   return rate;
-}
-template<class R>
-HTR_DEV void scatterFast(const R &r, double rate, double *w) {
-   HTR_UNROLL
-   for (int i = 0; i < HTR_MAX_REACTANTS; i++)
-      if (i < r.Neducts) {
-         const double d = r.educts[i].nu*rate;
-         HTR_UNROLL
-         for (int s = 0; s < nSpec; s++) if (r.educts[i].ind == s) w[s] -= d;
-      }
-   HTR_UNROLL
-   for (int i = 0; i < HTR_MAX_PRODUCTS; i++)
-      if (i < r.Npducts) {
-         const double d = r.pducts[i].nu*rate;
-         HTR_UNROLL
-         for (int s = 0; s < nSpec; s++) if (r.pducts[i].ind == s) w[s] += d;
-      }
-}
+//   * the structure of the mechanism (species indices, stoichiometric coefficients, which Arrhenius terms
+//     exist) is compile-time (generated/<Mix>_mechanism.inc), so every array index is a literal after
+//     unrolling: no local memory, no select chains; nu = 2 is a multiplication.
+HTR_DEV double powNu(double c, float nu) { return (nu == 1.0f) ? c : ((nu == 2.0f) ? c*c : pow(c, (double)nu)); }
 HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, const double *Yi) {
+   // structure of the mechanism as compile-time tables (generated/<Mix>_mechanism.inc); htr_set_mixture
+   // refuses a mixture block whose reaction tables differ from the ones these were generated from
+#if defined(HTR_MIX_AirMix)
+#include "generated/AirMix_mechanism.inc"
+#endif
+   static_assert(MECH_NR == HTR_NREAC + HTR_NTBREAC, "mechanism tables out of date");
    const double T = Tn*c_mix.TRef;
    const double P = Pn*c_mix.PRef;
    const double rho = rhon*c_mix.rhoRef;
@@ -434,25 +388,40 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
       C[i] = Yi[i]*rho/c_mix.species[i].W;
       G[i] = spec::GetFreeEnthalpy(c_mix.species[i], c_der[i], T, iT, logT);
    }
-#if HTR_NREAC > 0
+   const double cM = P/(RGAS*T);
    HTR_UNROLL
-   for (int r = 0; r < HTR_NREAC; r++)
-      scatterFast(c_mix.reactions[r], netRateFast(c_mix.reactions[r], logT, iT, logTRP, C, G), w);
-#endif
-#if HTR_NTBREAC > 0
-   HTR_UNROLL
-   for (int r = 0; r < HTR_NTBREAC; r++) {
-      const CollisionReaction &R = c_mix.tbReactions[r];
-      double c = 1.0;
-      if (R.Nthirdb > 0) {
-         c = P/(RGAS*T);
+   for (int r = 0; r < MECH_NR; r++) {
+      const Arrhenius k = (r < HTR_NREAC) ? c_mix.reactions[r < HTR_NREAC ? r : 0].k
+                                          : c_mix.tbReactions[r >= HTR_NREAC ? r - HTR_NREAC : 0].k;
+      double ex = 0.0;
+      if (MECH_HASN[r]) ex += k.n*logT;
+      if (MECH_HASE[r]) ex -= k.EovR*iT;
+      double a = 1.0;
+      HTR_UNROLL
+      for (int i = 0; i < HTR_MAX_REACTANTS; i++) if (i < MECH_NE[r]) a *= powNu(C[MECH_EI[r][i]], MECH_EN[r][i]);
+      double rate = k.A*exp(ex)*a;
+      if (MECH_BW[r]) {
+         double sumNu = 0.0, sumNuG = 0.0, b = 1.0;
          HTR_UNROLL
-         for (int i = 0; i < HTR_MAX_TB; i++)
-            if (i < R.Nthirdb) c += pick(C, R.thirdb[i].ind)*(R.thirdb[i].nu - 1.0);
+         for (int i = 0; i < HTR_MAX_REACTANTS; i++) if (i < MECH_NE[r]) { sumNu -= MECH_EN[r][i]; sumNuG -= MECH_EN[r][i]*G[MECH_EI[r][i]]; }
+         HTR_UNROLL
+         for (int i = 0; i < HTR_MAX_PRODUCTS; i++) if (i < MECH_NP[r]) {
+            sumNu += MECH_PN[r][i]; sumNuG += MECH_PN[r][i]*G[MECH_PI[r][i]];
+            b *= powNu(C[MECH_PI[r][i]], MECH_PN[r][i]);
+         }
+         rate -= k.A*exp(ex + sumNuG + sumNu*logTRP)*b;
       }
-      scatterFast(R, c*netRateFast(R, logT, iT, logTRP, C, G), w);
+      if (r >= HTR_NREAC && MECH_NT[r] > 0) {
+         double c = cM;
+         HTR_UNROLL
+         for (int i = 0; i < HTR_MAX_TB; i++) if (i < MECH_NT[r]) c += C[MECH_TI[r][i]]*(MECH_TN[r][i] - 1.0);
+         rate *= c;
+      }
+      HTR_UNROLL
+      for (int i = 0; i < HTR_MAX_REACTANTS; i++) if (i < MECH_NE[r]) w[MECH_EI[r][i]] -= MECH_EN[r][i]*rate;
+      HTR_UNROLL
+      for (int i = 0; i < HTR_MAX_PRODUCTS; i++) if (i < MECH_NP[r]) w[MECH_PI[r][i]] += MECH_PN[r][i]*rate;
    }
-#endif
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) w[i] *= c_mix.species[i].W*c_mix.iwiRef;
 }

@@ -226,14 +226,16 @@ def test_ghost_layout_block_matches_periodic_tile(cfg, scheme, chem, kw):
                                          (AIR, True, {"species_wave": 1.0, "front": 0.3, "stretch": 0.1})], ids=["constprop", "air"])
 @pytest.mark.parametrize("scheme", ["Hybrid", "SkewSymmetric"])
 @pytest.mark.parametrize("variant", ["", "strict"], ids=["prod", "strict"])
-def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant):
+@pytest.mark.parametrize("n", [(45, 23, 19), (104, 20, 12)], ids=["odd", "bulk"])
+def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
     """htr_rhs through the shared-memory staged kernels (csrc/htr_fast.cuh) vs the same call with the
     per-task kernels ("fast" = 0), on a box whose sizes are no multiple of any tile and with a mixed
     sensor field (so smooth cells, deferred cells and their neighbours all occur).  Strict build: the
     two are the same sequence of IEEE operations per cell -> bit-identical, and both agree with the
     oracle; production build: they differ by FMA contraction only."""
+    # "odd": no size is a multiple of a tile and rows are not 16-byte aligned (cooperative loads);
+    # "bulk": rows eligible for the TMA bulk copies (csrc/htr_bulk.cuh), interior CTAs use them
     o = oracle_for(cfg)
-    n = (45, 23, 19)
     f = host_state(o, n, cfg, **kw)
     _sensors(o, f)
     if scheme == "Hybrid":
