@@ -104,6 +104,7 @@ def load_library(mix, variant=""):
     L.htr_update_conserved_from_primitive.argtypes = [vp, vp, vp]
     L.htr_max_spectral_radius.argtypes = [vp, vp, vp, vp]
     L.htr_rhs.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
+    L.htr_rhs_parts.argtypes = [i, i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
     assert L.htr_mixture_name().decode() == mix
     _LIBS[key] = L
@@ -283,6 +284,13 @@ class Solver:
         t, b = self._rects(fl, tile, bounds)
         self._check(self.L.htr_rhs(SCHEMES[scheme], int(diffusion), int(chemistry), C.byref(fl.struct()), t, b,
                                    RK_coeffs[0], RK_coeffs[1], deltaTime, self._stream()), "htr_rhs")
+
+    def UpdateDerivativesParts(self, parts, fl, scheme, diffusion=True, chemistry=False, RK_coeffs=(1.0, 0.0), deltaTime=0.0,
+                               tile=None, bounds=None):
+        """Some of the staged kernels of UpdateDerivatives (htr_rhs_parts; timing only)."""
+        t, b = self._rects(fl, tile, bounds)
+        self._check(self.L.htr_rhs_parts(int(parts), SCHEMES[scheme], int(diffusion), int(chemistry), C.byref(fl.struct()), t, b,
+                                         RK_coeffs[0], RK_coeffs[1], deltaTime, self._stream()), "htr_rhs_parts")
 
     # host-buffer stage: torch CPU (pinned) tensors in, Conserved_t out; see htr_host_rhs in include/htr_b200.h
     def HostRHS(self, fl, scheme, h_Conserved, h_temperature, h_Conserved_t, h_Conserved_old=None, diffusion=True,

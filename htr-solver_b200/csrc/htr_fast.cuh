@@ -30,13 +30,27 @@
 
 // resident CTAs per SM the register allocation aims at (tuned on B200 with ncu, see profiles/)
 #ifndef HTR_K1_MINB
-#define HTR_K1_MINB 2
+#define HTR_K1_MINB 1
 #endif
 #ifndef HTR_K2_MINB
-#define HTR_K2_MINB 2
+#define HTR_K2_MINB 3
 #endif
 #ifndef HTR_D_MINB
 #define HTR_D_MINB 3
+#endif
+
+// tile heights (rows of 32 cells) of the in-plane Euler kernel and of the diffusion kernels
+#ifndef HTR_K2_TY
+#define HTR_K2_TY 8
+#endif
+#ifndef HTR_D_TJ
+#define HTR_D_TJ 8
+#endif
+#ifndef HTR_DB_MINB
+#define HTR_DB_MINB 2
+#endif
+#ifndef HTR_D_HOIST
+#define HTR_D_HOIST 0
 #endif
 
 namespace htr {
@@ -480,7 +494,7 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    const bool upd = inTile && j >= 1 && (!DOX || i >= 1);
    double *Ct = at<double>(f.Conserved_t, c);
    double ct[nEq], mJ = 0.0, mx = 0.0;
-   if (upd) {
+   if (HTR_D_HOIST && upd) {
       HTR_UNROLL
       for (int e = 0; e < nEq; e++) ct[e] = Ct[e];
       mJ = ld<double>(m_dOf<JD>(f), c);
@@ -528,6 +542,12 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    __syncthreads();
    if (upd) {
       if (ok) {
+         if (!HTR_D_HOIST) {
+            HTR_UNROLL
+            for (int e = 0; e < nEq; e++) ct[e] = Ct[e];
+            mJ = ld<double>(m_dOf<JD>(f), c);
+            if (DOX) mx = ld<double>(f.dcsi_d, c);
+         }
          HTR_UNROLL
          for (int e = 0; e < nEq; e++) {
             double v = ct[e];

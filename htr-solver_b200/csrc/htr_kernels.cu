@@ -18,6 +18,7 @@
 #include "htr_pointwise.cuh"
 #include "htr_fast.cuh"
 #include "htr_fast_bulk.cuh"
+#include "htr_diff_bulk.cuh"
 
 namespace htr {
 
@@ -172,6 +173,8 @@ static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const 
 // Fast path of  Conserved_t = 0 (+chem) + Euler z,y,x  for the Hybrid and SkewSymmetric schemes
 // (htr_fast.cuh) followed by the masked generic kernels for the cells it deferred.
 // `scratch` holds two mask bytes per cell of the tile.
+static bool g_bulk_diffusion = false;   // htr_set_option("bulk_diffusion", 1): TMA bulk staging for the diffusion kernels too
+static bool g_no_pipe = false;          // htr_set_option("pipeline", 0): htr_host_rhs without the z-slab copy/compute overlap
 static bool g_no_bulk = false;          // htr_set_option("bulk", 0): cooperative loads instead of TMA bulk copies
 
 // Can rows of these fields be moved by cp.async.bulk?  Returns 0 (no) or 1 | parity<<1 (htr_bulk.cuh).
@@ -188,11 +191,13 @@ static int bulkEligible(std::initializer_list<std::pair<const htr_acc*, int>> fi
    return 1 | (parity << 1);
 }
 
+enum { PART_EZ = 1, PART_EXY = 2, PART_DZ = 4, PART_DXY = 8, PART_ALL = 15 };
+
 template<int SCHEME>
 static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
-                                   const EulerParams &ep, uint8_t *scratch, cudaStream_t st) {
+                                   const EulerParams &ep, uint8_t *scratch, cudaStream_t st, int parts = PART_ALL) {
    constexpr bool HY = (SCHEME == HTR_SCHEME_HYBRID);
-   constexpr int TY = 8;
+   constexpr int TY = HTR_K2_TY;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
    int *flags = reinterpret_cast<int*>(scratch);      // cells deferred by: [0] Euler z, [1] Euler xy, [2] diffusion z, [3] diffusion xy
    uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
@@ -204,7 +209,7 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
       cudaFuncSetAttribute(fast::euler_xy_bulk_kernel<TY, HY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::XYB<TY>::SMEM);
       attr = true;
    }
-   {
+   if (parts & PART_EZ) {
       dim3 grid((unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1], (unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)));
       dim3 block(fast::ZT_X, fast::ZT_Z, 1);
       if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
@@ -213,7 +218,7 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
       if (e != cudaSuccess) return e;
       if ((e = launchMasked<2, FLUX_EULER, SCHEME>(f, tile, B, ep, maskZ, flags, st)) != cudaSuccess) return e;
    }
-   {
+   if (parts & PART_EXY) {
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TY - 2)/(TY - 1)), (unsigned)n[2]);
       dim3 block(32, TY, 1);
       const int bulkOK = bulkEligible({{&f.rho, 1}, {&f.pressure, 1}, {&f.velocity, 3}, {&f.MassFracs, nSpec}});
@@ -228,28 +233,53 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
 
 // Conserved_t += diffusion z; += y; += x through the staged kernels + masked generic passes (same scratch,
 // after launchFastEuler has consumed it in stream order; flags [2], [3] were cleared there).
-static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, uint8_t *scratch, cudaStream_t st) {
-   constexpr int TJ = 8;
+static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, uint8_t *scratch, cudaStream_t st,
+                                       int parts = PART_ALL) {
+   constexpr int TJ = HTR_D_TJ;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
    int *flags = reinterpret_cast<int*>(scratch);
    uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
    const EulerParams ep = {0, 0, 0};
    static bool attr = false;
    if (!attr) {
-      cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
-      cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
+      cudaFuncSetAttribute(fast::diffusion_bulk_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<2, TJ>::SMEM);
+      cudaFuncSetAttribute(fast::diffusion_bulk_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<1, TJ>::SMEM);
       attr = true;
    }
    cudaError_t e;
-   {
+   if (!g_bulk_diffusion) {
+      // default: cooperative staging (htr_fast.cuh).  Measured on B200 (profiles/r1_v8_*): the bulk-copy variant below
+      // needs ~90 row copies of 0.3-2.6 KB per CTA and is TMA-issue bound (Dz 3.2 vs 1.9 ms, Dxy 4.2 vs 3.3 ms at 256^3).
+      static bool attr2 = false;
+      if (!attr2) {
+         cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
+         cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
+         attr2 = true;
+      }
+      dim3 gz((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
+      if (parts & PART_DZ) {
+         fast::diffusion_staged_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(f, tile, B, maskZ, flags + 2);
+         if ((e = cudaGetLastError()) != cudaSuccess) return e;
+         if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
+      }
+      if (!(parts & PART_DXY)) return cudaSuccess;
+      dim3 gxy((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
+      fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(f, tile, B, maskXY, flags + 3);
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st);
+   }
+   const int bulkOK = bulkEligible({{&f.rho, 1}, {&f.mu, 1}, {&f.lam, 1}, {&f.temperature, 1}, {&f.MolarFracs, nSpec},
+                                    {&f.Di, nSpec}, {&f.Conserved, nEq}, {&f.velocity, 3}});
+   if (parts & PART_DZ) {
       dim3 grid((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
-      fast::diffusion_staged_kernel<2, TJ><<<grid, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(f, tile, B, maskZ, flags + 2);
+      fast::diffusion_bulk_kernel<2, TJ><<<grid, dim3(32, TJ, 1), fast::DB<2, TJ>::SMEM, st>>>(f, tile, B, maskZ, flags + 2, bulkOK);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
    }
-   {
+   if (parts & PART_DXY) {
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
-      fast::diffusion_staged_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(f, tile, B, maskXY, flags + 3);
+      fast::diffusion_bulk_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DB<1, TJ>::SMEM, st>>>(f, tile, B, maskXY, flags + 3, bulkOK);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
       if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
@@ -530,6 +560,8 @@ int htr_set_option(const char *name, int value) {
    if (!name) return HTR_EINVAL;
    if (strcmp(name, "fast") == 0) { g_no_fast = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
+   if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
+   if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
    return HTR_EINVAL;
 }
 
@@ -687,6 +719,11 @@ int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_
 
 int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
             const htr_rect *bounds, double RK0, double RK1, double deltaTime, void *stream) {
+   return htr_rhs_parts(PART_ALL, scheme, diffusion, chemistry, f, tile, bounds, RK0, RK1, deltaTime, stream);
+}
+
+int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
+                  const htr_rect *bounds, double RK0, double RK1, double deltaTime, void *stream) {
    HTR_CHECK_COMMON(f, tile)
    if (!bounds) return HTR_EINVAL;
    // Reference task order (src/prometeo.rg:502-578): 0, +chem, +Euler z,y,x, +diffusion z,y,x.
@@ -698,12 +735,13 @@ int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const 
       if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
       const EulerParams ep = {RK0, RK1, deltaTime};
       cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
-         ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st)
-         : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st);
+         ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st, parts)
+         : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st, parts);
       if (e != cudaSuccess) return cuerr(e);
-      if (diffusion && (e = launchFastDiffusion(*f, *tile, *bounds, scratch, st)) != cudaSuccess) return cuerr(e);
+      if (diffusion && (e = launchFastDiffusion(*f, *tile, *bounds, scratch, st, parts)) != cudaSuccess) return cuerr(e);
       return HTR_OK;
    }
+   if (parts != PART_ALL) return HTR_EINVAL;      // the per-task sequence below is not split
    {  // Conserved_t = 0 over the tile (RK.InitializeTimeDerivatives, src/prometeo_rk.rg:61-87)
       zero_rhs_kernel<<<blocksFor(*tile, 128), 128, 0, st>>>(*f, *tile);
       cudaError_t e = cudaGetLastError();
@@ -733,6 +771,26 @@ static void *cellPtr(const htr_acc &a, const htr_rect &t) {
    return static_cast<char*>(a.base) + t.lo[0]*a.stride[0] + t.lo[1]*a.stride[1] + t.lo[2]*a.stride[2];
 }
 
+// z-slab pipeline of htr_host_rhs: uploads (copy stream), device work (caller's stream) and downloads (second copy
+// stream) of different slabs overlap.  Stage dependencies across slabs (stencil reach 3 planes < slab thickness):
+//   P(k) primitives+properties  <- upload k           D(k) Ducros       <- P(k-1..k+1)
+//   S(k) shock sensors          <- D(k-1..k+1)        R(k) htr_rhs      <- S(k-1..k+1), P(k-1..k+1)
+// Slab neighbours are taken modulo the slab count (periodic boxes wrap; for bounded boxes this only delays work).
+struct HostPipe { cudaStream_t up, down; cudaEvent_t evUp[16], evR[16], evStart, evDone; bool ok; };
+static HostPipe g_pipe = {};
+static bool pipeInit() {
+   if (g_pipe.ok) return true;
+   if (cudaStreamCreateWithFlags(&g_pipe.up, cudaStreamNonBlocking) != cudaSuccess) return false;
+   if (cudaStreamCreateWithFlags(&g_pipe.down, cudaStreamNonBlocking) != cudaSuccess) return false;
+   for (int i = 0; i < 16; i++)
+      if (cudaEventCreateWithFlags(&g_pipe.evUp[i], cudaEventDisableTiming) != cudaSuccess ||
+          cudaEventCreateWithFlags(&g_pipe.evR[i], cudaEventDisableTiming) != cudaSuccess) return false;
+   if (cudaEventCreateWithFlags(&g_pipe.evStart, cudaEventDisableTiming) != cudaSuccess) return false;
+   if (cudaEventCreateWithFlags(&g_pipe.evDone, cudaEventDisableTiming) != cudaSuccess) return false;
+   g_pipe.ok = true;
+   return true;
+}
+
 int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, double vorticityScale,
                  const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds,
                  const double *h_Conserved, const double *h_Conserved_old, double *h_temperature,
@@ -742,25 +800,89 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
    if (!denseField(f->Conserved, *tile, 8*nEq) || !denseField(f->Conserved_t, *tile, 8*nEq) ||
        !denseField(f->temperature, *tile, 8) || !denseField(f->Conserved_old, *tile, 8*nEq)) return HTR_EINVAL;
    cudaStream_t st = (cudaStream_t)stream;
-   const size_t cells = (size_t)(tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
+   const int64_t nx = tile->hi[0] - tile->lo[0] + 1, ny = tile->hi[1] - tile->lo[1] + 1, nz = tile->hi[2] - tile->lo[2] + 1;
+   const bool needOld = (nSpec > 1 && scheme != HTR_SCHEME_SKEWSYMMETRIC);
+   const bool sensors = update_sensors && scheme == HTR_SCHEME_HYBRID;
+   const int ns = (nz >= 128 && !g_no_pipe && pipeInit()) ? 16 : 1;
    cudaError_t e;
-   if ((e = cudaMemcpyAsync(cellPtr(f->Conserved, *tile), h_Conserved, cells*8*nEq, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuerr(e);
-   if (nSpec > 1 && scheme != HTR_SCHEME_SKEWSYMMETRIC) {
-      const double *src = h_Conserved_old ? h_Conserved_old : h_Conserved;
-      if ((e = cudaMemcpyAsync(cellPtr(f->Conserved_old, *tile), src, cells*8*nEq, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuerr(e);
-   }
-   if ((e = cudaMemcpyAsync(cellPtr(f->temperature, *tile), h_temperature, cells*8, cudaMemcpyHostToDevice, st)) != cudaSuccess) return cuerr(e);
    int rc;
-   if ((rc = htr_update_primitive_from_conserved(f, tile, stream)) != HTR_OK) return rc;
-   if ((rc = htr_update_properties_from_primitive(f, tile, stream)) != HTR_OK) return rc;
-   if (update_sensors && scheme == HTR_SCHEME_HYBRID) {
-      if ((rc = htr_ducros_sensor(f, tile, bounds, vorticityScale, stream)) != HTR_OK) return rc;
-      for (int d = 0; d < 3; d++)
-         if ((rc = htr_shock_sensor(d, f, tile, bounds, stream)) != HTR_OK) return rc;
+   auto slab = [&](int k) {           // z range of slab k (modulo ns)
+      k = ((k % ns) + ns) % ns;
+      htr_rect r = *tile;
+      r.lo[2] = tile->lo[2] + nz*k/ns;
+      r.hi[2] = tile->lo[2] + nz*(k + 1)/ns - 1;
+      return r;
+   };
+   auto upload = [&](int k, cudaStream_t s) -> cudaError_t {
+      const htr_rect r = slab(k);
+      const size_t off = (size_t)(r.lo[2] - tile->lo[2])*nx*ny, cells = (size_t)(r.hi[2] - r.lo[2] + 1)*nx*ny;
+      cudaError_t q;
+      if ((q = cudaMemcpyAsync(cellPtr(f->Conserved, r), h_Conserved + off*nEq, cells*8*nEq, cudaMemcpyHostToDevice, s)) != cudaSuccess) return q;
+      if (needOld && h_Conserved_old &&
+          (q = cudaMemcpyAsync(cellPtr(f->Conserved_old, r), h_Conserved_old + off*nEq, cells*8*nEq, cudaMemcpyHostToDevice, s)) != cudaSuccess) return q;
+      return cudaMemcpyAsync(cellPtr(f->temperature, r), h_temperature + off, cells*8, cudaMemcpyHostToDevice, s);
+   };
+   auto download = [&](int k, cudaStream_t s) -> cudaError_t {
+      const htr_rect r = slab(k);
+      const size_t off = (size_t)(r.lo[2] - tile->lo[2])*nx*ny, cells = (size_t)(r.hi[2] - r.lo[2] + 1)*nx*ny;
+      cudaError_t q;
+      if ((q = cudaMemcpyAsync(h_Conserved_t + off*nEq, cellPtr(f->Conserved_t, r), cells*8*nEq, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return q;
+      return cudaMemcpyAsync(h_temperature + off, cellPtr(f->temperature, r), cells*8, cudaMemcpyDeviceToHost, s);
+   };
+   auto P = [&](int k) -> int {
+      const htr_rect r = slab(k);
+      int q;
+      if ((q = htr_update_primitive_from_conserved(f, &r, stream)) != HTR_OK) return q;
+      if ((q = htr_update_properties_from_primitive(f, &r, stream)) != HTR_OK) return q;
+      if (needOld && !h_Conserved_old) {       // no separate old state: device copy instead of a second upload
+         const size_t cells = (size_t)(r.hi[2] - r.lo[2] + 1)*nx*ny;
+         if (cudaMemcpyAsync(cellPtr(f->Conserved_old, r), cellPtr(f->Conserved, r), cells*8*nEq, cudaMemcpyDeviceToDevice, st) != cudaSuccess) return 1000;
+      }
+      return HTR_OK;
+   };
+   auto D = [&](int k) -> int { const htr_rect r = slab(k); return sensors ? htr_ducros_sensor(f, &r, bounds, vorticityScale, stream) : HTR_OK; };
+   auto S = [&](int k) -> int {
+      if (!sensors) return HTR_OK;
+      const htr_rect r = slab(k);
+      for (int d = 0; d < 3; d++) { const int q = htr_shock_sensor(d, f, &r, bounds, stream); if (q != HTR_OK) return q; }
+      return HTR_OK;
+   };
+   auto R = [&](int k) -> int { const htr_rect r = slab(k); return htr_rhs(scheme, diffusion, chemistry, f, &r, bounds, RK0, RK1, deltaTime, stream); };
+
+   if (ns == 1) {
+      if ((e = upload(0, st)) != cudaSuccess) return cuerr(e);
+      if ((rc = P(0)) != HTR_OK || (rc = D(0)) != HTR_OK || (rc = S(0)) != HTR_OK || (rc = R(0)) != HTR_OK) return rc;
+      return cuerr(download(0, st));
    }
-   if ((rc = htr_rhs(scheme, diffusion, chemistry, f, tile, bounds, RK0, RK1, deltaTime, stream)) != HTR_OK) return rc;
-   if ((e = cudaMemcpyAsync(h_Conserved_t, cellPtr(f->Conserved_t, *tile), cells*8*nEq, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuerr(e);
-   if ((e = cudaMemcpyAsync(h_temperature, cellPtr(f->temperature, *tile), cells*8, cudaMemcpyDeviceToHost, st)) != cudaSuccess) return cuerr(e);
+   // the copy streams start after whatever the caller queued before this call
+   if ((e = cudaEventRecord(g_pipe.evStart, st)) != cudaSuccess) return cuerr(e);
+   cudaStreamWaitEvent(g_pipe.up, g_pipe.evStart, 0);
+   cudaStreamWaitEvent(g_pipe.down, g_pipe.evStart, 0);
+   for (int k = 0; k < ns; k++) {
+      if ((e = upload(k, g_pipe.up)) != cudaSuccess) return cuerr(e);
+      cudaEventRecord(g_pipe.evUp[k], g_pipe.up);
+   }
+   auto finish = [&](int k) -> int {          // R(k) then its download
+      int q = R(k);
+      if (q != HTR_OK) return q;
+      cudaEventRecord(g_pipe.evR[k], st);
+      cudaStreamWaitEvent(g_pipe.down, g_pipe.evR[k], 0);
+      return cuerr(download(k, g_pipe.down));
+   };
+   // stage s of slab j may run once stage s-1 of j-1, j, j+1 has been issued (same stream: issue order = execution order)
+   for (int k = 0; k < ns; k++) {
+      cudaStreamWaitEvent(st, g_pipe.evUp[k], 0);
+      if ((rc = P(k)) != HTR_OK) return rc;
+      if (k >= 2 && (rc = D(k - 1)) != HTR_OK) return rc;              // D(1 .. ns-2)
+      if (k >= 4 && (rc = S(k - 2)) != HTR_OK) return rc;              // S(2 .. ns-3)
+      if (k >= 6 && (rc = finish(k - 3)) != HTR_OK) return rc;         // R(3 .. ns-4)
+   }
+   if ((rc = D(ns - 1)) != HTR_OK || (rc = D(0)) != HTR_OK) return rc;
+   if ((rc = S(ns - 2)) != HTR_OK || (rc = S(ns - 1)) != HTR_OK || (rc = S(0)) != HTR_OK || (rc = S(1)) != HTR_OK) return rc;
+   for (int k : {ns - 3, ns - 2, ns - 1, 0, 1, 2})
+      if ((rc = finish(k)) != HTR_OK) return rc;
+   cudaEventRecord(g_pipe.evDone, g_pipe.down);
+   cudaStreamWaitEvent(st, g_pipe.evDone, 0);
    return HTR_OK;
 }
 

@@ -116,6 +116,12 @@ int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_
 int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
             const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
 
+/* The same pass restricted to some of its staged kernels (timing / profiling only: a partial pass leaves
+ * Conserved_t incomplete).  parts = bit mask: 1 Conserved_t = 0 + chem + Euler z; 2 += Euler y, x; 4 += diffusion z;
+ * 8 += diffusion y, x.  15 = htr_rhs.  Hybrid and SkewSymmetric schemes with the "fast" option on. */
+int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
+                  const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+
 /* ---- host-buffer stage (the call a host-resident driver binds) ----
  * h_* are HOST pointers (pinned for full copy bandwidth), dense [z][y][x][comp] over `tile`.
  * Copies Conserved (and Conserved_old for the multispecies limiter; NULL = same as Conserved) and the
