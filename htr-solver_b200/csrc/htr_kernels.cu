@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <math.h>
 #include <initializer_list>
 #include <utility>
 #include "htr_euler.cuh"
@@ -615,6 +616,39 @@ int htr_set_mixture(const void *mix, size_t bytes) {
          }
       }
       e = cudaMemcpyToSymbol(c_der, der, sizeof(der));
+      // transport constants (reference expressions: Species.inl GetMu/GetDif/GetSelfDiffusion/GetFZrot, MultiComponent.inl GetViscosity)
+      TransDerived tr;
+      memset(&tr, 0, sizeof(tr));
+      tr.pi15 = pow(PI, 1.5); tr.kb3 = pow(kb, 3);
+      for (int i = 0; i < nSpec; i++) {
+         const SpeciesData &a = m.species[i];
+         tr.sigma2[i] = pow(a.diff.sigma, 2);
+         const double tmp = 1.0/(a.diff.kbOveps*298.0);
+         tr.fz298[i] = 1 + 0.5*pow(PI, 1.5)*sqrt(tmp) + (2 + 0.25*PI*PI)*tmp + pow(PI, 1.5)*pow(tmp, 1.5);
+         for (int j = 0; j < nSpec; j++) {
+            const SpeciesData &b = m.species[j];
+            tr.w25[i][j] = pow(b.W/a.W, 0.25);
+            tr.s8[i][j] = sqrt(8*(1 + a.W/b.W));
+            double xi = 1.0;
+            if ((a.diff.mu*b.diff.mu == 0.0) && (a.diff.mu + b.diff.mu != 0.0)) {
+               double mup, alp, epr;
+               if (a.diff.mu != 0.0) {
+                  mup = a.diff.mu/sqrt(4*PI*eps_0*kb*pow(a.diff.sigma, 3)/a.diff.kbOveps);
+                  alp = b.diff.alpha/pow(b.diff.sigma, 3);
+                  epr = sqrt(b.diff.kbOveps/a.diff.kbOveps);
+               } else {
+                  mup = b.diff.mu/sqrt(4*PI*eps_0*kb*pow(b.diff.sigma, 3)/b.diff.kbOveps);
+                  alp = a.diff.alpha/pow(a.diff.sigma, 3);
+                  epr = sqrt(a.diff.kbOveps/b.diff.kbOveps);
+               }
+               xi = 1 + 0.25*mup*alp*epr;
+            }
+            tr.sigmaij[i][j] = 0.5*(a.diff.sigma + b.diff.sigma)*pow(xi, -1./6);
+            tr.kboEpsij[i][j] = sqrt(a.diff.kbOveps*b.diff.kbOveps)/(xi*xi);
+            tr.invWij[i][j] = (a.W + b.W)/(a.W*b.W);
+         }
+      }
+      if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_tr, &tr, sizeof(tr));
    }
 #endif
    if (e == cudaSuccess) g_mix_loaded = true;

@@ -16,6 +16,20 @@ __constant__ MixData c_mix;
 // (src/Mixtures/Species.inl: RGAS/W, cp[3]*0.50, cp[4]/3, cp[5]*0.25, cp[6]/5, cp[5]/6) for the ranges H, M, L.
 struct SpecDerived { double rOvW; double q[3][5]; };
 __constant__ SpecDerived c_der[HTR_NSPEC];
+// Temperature-independent parts of the transport models (src/Mixtures/Species.inl:205-357, MultiComponent.inl:150-260),
+// evaluated once on the host with the reference's expressions and libm (htr_set_mixture): powers and roots of
+// collision diameters, molar-weight ratios and well depths that the reference recomputes per cell.
+struct TransDerived {
+   double sigma2[HTR_NSPEC];                 // pow(sigma, 2)
+   double fz298[HTR_NSPEC];                  // GetFZrot(298)
+   double w25[HTR_NSPEC][HTR_NSPEC];         // pow(W[j]/W[i], 0.25)
+   double s8[HTR_NSPEC][HTR_NSPEC];          // sqrt(8*(1 + W[i]/W[j]))
+   double sigmaij[HTR_NSPEC][HTR_NSPEC];     // Stockmayer-corrected pair diameter, i > j
+   double kboEpsij[HTR_NSPEC][HTR_NSPEC];
+   double invWij[HTR_NSPEC][HTR_NSPEC];
+   double pi15, kb3;                         // pow(PI, 1.5), pow(kb, 3)
+};
+__constant__ TransDerived c_tr;
 #endif
 
 #define HTR_DEV __device__ __forceinline__
@@ -104,56 +118,55 @@ HTR_DEV double omega_D(double T) {
    const double den = 1.45337701568 + T*(5.2269794238 + T*(9.7108519575 + T*(0.46539437353 + T*0.00041908394781)));
    return num/den;
 }
-HTR_DEV double GetMu(const SpeciesData &s, double T) {
+// T^3 and x^1.5: libdevice pow in the strict build (the reference calls pow), products otherwise
+HTR_DEV double cube(double x) {
+#ifdef HTR_EXACT_POW
+   return pow(x, 3);
+#else
+   return x*x*x;
+#endif
+}
+HTR_DEV double pow15(double x) {
+#ifdef HTR_EXACT_POW
+   return pow(x, 1.5);
+#else
+   return x*sqrt(x);
+#endif
+}
+HTR_DEV double GetMu(const SpeciesData &s, int i, double T) {
    const double num = 5*sqrt(PI*s.W/Na*kb*T);
-   const double den = 16*PI*pow(s.diff.sigma, 2)*omega_mu(T*s.diff.kbOveps);
+   const double den = 16*PI*c_tr.sigma2[i]*omega_mu(T*s.diff.kbOveps);
    return num/den;
 }
-// Stockmayer-corrected binary diffusion coefficient of the pair (a, b)
-HTR_DEV double GetDif(const SpeciesData &a, const SpeciesData &b, double P, double T) {
-   double xi = 1.0;
-   if ((a.diff.mu*b.diff.mu == 0.0) && (a.diff.mu + b.diff.mu != 0.0)) {
-      double mup, alp, epr;     // polar / non-polar pair
-      if (a.diff.mu != 0.0) {
-         mup = a.diff.mu/sqrt(4*PI*eps_0*kb*pow(a.diff.sigma, 3)/a.diff.kbOveps);
-         alp = b.diff.alpha/pow(b.diff.sigma, 3);
-         epr = sqrt(b.diff.kbOveps/a.diff.kbOveps);
-      } else {
-         mup = b.diff.mu/sqrt(4*PI*eps_0*kb*pow(b.diff.sigma, 3)/b.diff.kbOveps);
-         alp = a.diff.alpha/pow(a.diff.sigma, 3);
-         epr = sqrt(a.diff.kbOveps/b.diff.kbOveps);
-      }
-      xi = 1 + 0.25*mup*alp*epr;
-   }
-   const double sigmaij = 0.5*(a.diff.sigma + b.diff.sigma)*pow(xi, -1./6);
-   const double kboEpsij = sqrt(a.diff.kbOveps*b.diff.kbOveps)/(xi*xi);
-   const double omega11 = omega_D(T*kboEpsij);
-   const double invWij = (a.W + b.W)/(a.W*b.W);
-   const double num = 3*sqrt(2*PI*pow(kb, 3)*pow(T, 3)*Na*invWij);
+// Stockmayer-corrected binary diffusion coefficient of the pair (i, j), i > j; T3 = T^3
+HTR_DEV double GetDif(int i, int j, double P, double T3, double T) {
+   const double sigmaij = c_tr.sigmaij[i][j];
+   const double omega11 = omega_D(T*c_tr.kboEpsij[i][j]);
+   const double num = 3*sqrt(2*PI*c_tr.kb3*T3*Na*c_tr.invWij[i][j]);
    const double den = 16*PI*P*sigmaij*sigmaij*omega11;
    return num/den;
 }
-HTR_DEV double GetSelfDiffusion(const SpeciesData &s, double T) {
+HTR_DEV double GetSelfDiffusion(const SpeciesData &s, int i, double T) {
    const double num = 3*sqrt(PI*kb*T*s.W/Na);
-   const double den = 8*PI*pow(s.diff.sigma, 2)*omega_D(T*s.diff.kbOveps);
+   const double den = 8*PI*c_tr.sigma2[i]*omega_D(T*s.diff.kbOveps);
    return num/den;
 }
 HTR_DEV double GetFZrot(const SpeciesData &s, double T) {
    const double tmp = 1.0/(s.diff.kbOveps*T);
-   return 1 + 0.5*pow(PI, 1.5)*sqrt(tmp) + (2 + 0.25*PI*PI)*tmp + pow(PI, 1.5)*pow(tmp, 1.5);
+   return 1 + 0.5*c_tr.pi15*sqrt(tmp) + (2 + 0.25*PI*PI)*tmp + c_tr.pi15*pow15(tmp);
 }
 // Species conductivity: monatomic (Eucken 15/4) or modified-Eucken with rotational relaxation
-HTR_DEV double GetLam(const SpeciesData &s, const SpecDerived &d, double T) {
-   const double mu = GetMu(s, T);
+HTR_DEV double GetLam(const SpeciesData &s, const SpecDerived &d, int i, double T) {
+   const double mu = GetMu(s, i, T);
    if (s.diff.Geom == 0) return 15.0/4*mu*RGAS/s.W;
    const bool lin = (s.diff.Geom == 1);
    const double CvROvR = lin ? 1.0 : 1.5;
    const double CvT = 1.5*RGAS;
    const double CvR = CvROvR*RGAS;
    const double CvV = GetCp(s, d, T)*s.W - (lin ? 3.5 : 4.0)*RGAS;
-   const double Dkk = GetSelfDiffusion(s, T);
+   const double Dkk = GetSelfDiffusion(s, i, T);
    const double fV = Dkk/mu;
-   const double Zrot = s.diff.Z298*GetFZrot(s, 298.0)/GetFZrot(s, T);
+   const double Zrot = s.diff.Z298*c_tr.fz298[i]/GetFZrot(s, T);
    const double A = 2.5 - fV;
    const double B = Zrot + 2/PI*(5./3*CvROvR + fV);
    const double fT = 2.5*(1. - 2*CvR*A/(PI*CvT*B));
@@ -249,15 +262,15 @@ HTR_DEV double GetViscosity(double Tn, const double *Xi) {
    const double T = Tn*c_mix.TRef;
    double muk[nSpec];
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) muk[i] = spec::GetMu(c_mix.species[i], T);
+   for (int i = 0; i < nSpec; i++) muk[i] = spec::GetMu(c_mix.species[i], i, T);
    double mu = 0.0;
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
       double den = 0.0;
       HTR_UNROLL
       for (int j = 0; j < nSpec; j++) {
-         double Phi = 1 + sqrt(muk[i]/muk[j])*pow(c_mix.species[j].W/c_mix.species[i].W, 0.25);
-         Phi *= Phi/sqrt(8*(1 + c_mix.species[i].W/c_mix.species[j].W));
+         double Phi = 1 + sqrt(muk[i]/muk[j])*c_tr.w25[i][j];
+         Phi *= Phi/c_tr.s8[i][j];
          den += Xi[j]*Phi;
       }
       mu += Xi[i]*muk[i]/den;
@@ -269,7 +282,7 @@ HTR_DEV double GetHeatConductivity(double Tn, const double *Xi) {
    double a = 0.0, b = 0.0;
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
-      const double lami = spec::GetLam(c_mix.species[i], c_der[i], T);
+      const double lami = spec::GetLam(c_mix.species[i], c_der[i], i, T);
       a += Xi[i]*lami;
       b += Xi[i]/lami;
    }
@@ -284,13 +297,14 @@ HTR_DEV double GetSpeedOfSound(double T, double gamma, double MixW) { return sqr
 HTR_DEV void GetDiffusivity(double *Di, double Pn, double Tn, double MixW, const double *Xi) {
    const double T = Tn*c_mix.TRef;
    const double P = Pn*c_mix.PRef;
+   const double T3 = spec::cube(T);
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) Di[i] = 0.0;
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
       HTR_UNROLL
       for (int j = 0; j < i; j++) {
-         const double invDij = 1.0/spec::GetDif(c_mix.species[i], c_mix.species[j], P, T);
+         const double invDij = 1.0/spec::GetDif(i, j, P, T3, T);
          Di[i] += Xi[j]*invDij;
          Di[j] += Xi[i]*invDij;
       }
