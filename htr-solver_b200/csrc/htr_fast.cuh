@@ -204,11 +204,31 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
          HTR_UNROLL
          for (int e = 0; e < nEq; e++) base[e] += mz*(F[e] - sF[e*ZT_NT + tid - ZT_X]);
       }
+      mask[maskIndex(c, tile)] = deferred;
+      if (deferred) *flag = 1;          // all writers store the same value
+   }
+   // Conserved_t rows leave through shared memory: a warp's 32 cells are nEq*32 consecutive doubles of the
+   // field, written as full 256-byte spans instead of nEq stores of 8 bytes at a 8*nEq-byte stride
+   if (f.Conserved_t.stride[0] == 8*nEq) {
+      __syncthreads();                                  // every warp has read its neighbour's flux from sF
+      double *sOut = smem + k*(nEq*ZT_X);
+      if (upd) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) sOut[i*nEq + e] = base[e];
+      }
+      __syncwarp();
+      if (k >= 1 && c.z <= tile.hi[2]) {                // warp-uniform: this row is updated
+         Pt r0 = c; r0.x = c.x - i;
+         const int64_t left = tile.hi[0] - r0.x + 1;
+         const int nval = nEq*(int)(left < ZT_X ? left : ZT_X);
+         double *row = at<double>(f.Conserved_t, r0);
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) { const int m = e*ZT_X + i; if (m < nval) row[m] = sOut[m]; }
+      }
+   } else if (upd) {
       double *Ct = at<double>(f.Conserved_t, c);
       HTR_UNROLL
       for (int e = 0; e < nEq; e++) Ct[e] = base[e];
-      mask[maskIndex(c, tile)] = deferred;
-      if (deferred) *flag = 1;          // all writers store the same value
    }
 }
 
@@ -541,23 +561,45 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    for (int e = 0; e < nEq; e++) sF[e*NT + tid] = FJ[e];
    __syncthreads();
    if (upd) {
+      if (!HTR_D_HOIST) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) ct[e] = Ct[e];
+         mJ = ld<double>(m_dOf<JD>(f), c);
+         if (DOX) mx = ld<double>(f.dcsi_d, c);
+      }
       if (ok) {
-         if (!HTR_D_HOIST) {
-            HTR_UNROLL
-            for (int e = 0; e < nEq; e++) ct[e] = Ct[e];
-            mJ = ld<double>(m_dOf<JD>(f), c);
-            if (DOX) mx = ld<double>(f.dcsi_d, c);
-         }
          HTR_UNROLL
          for (int e = 0; e < nEq; e++) {
             double v = ct[e];
             v += mJ*(FJ[e] - sF[e*NT + tid - 32]);
             if (DOX) v += mx*(Fx[e] - Fm[e]);
-            Ct[e] = v;
+            ct[e] = v;
          }
       }
       mask[maskIndex(c, tile)] = !ok;
       if (!ok) *flag = 1;
+   }
+   // rows of Conserved_t leave through shared memory as contiguous spans (a deferred tile rewrites its old values)
+   if (f.Conserved_t.stride[0] == 8*nEq) {
+      __syncthreads();
+      double *sOut = smem + j*(nEq*32);
+      constexpr int X0 = DOX ? 1 : 0, NXC = 32 - X0;      // first updated thread column, updated cells per row
+      if (upd) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) sOut[(i - X0)*nEq + e] = ct[e];
+      }
+      __syncwarp();
+      if (j >= 1 && cJ <= tile.hi[JD]) {
+         Pt r0 = c; r0.x = cx0 + X0;
+         const int64_t left = tile.hi[0] - r0.x + 1;
+         const int nval = nEq*(int)(left < NXC ? left : NXC);
+         double *row = at<double>(f.Conserved_t, r0);
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) { const int m = e*32 + i; if (m < nval) row[m] = sOut[m]; }
+      }
+   } else if (upd && ok) {
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) Ct[e] = ct[e];
    }
    (void)sFlag;
 }

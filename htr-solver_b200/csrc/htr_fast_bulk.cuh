@@ -203,19 +203,41 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
    }
    sFlag[tid] = hy;
    __syncthreads();
+   bool deferred = true;
    if (upd) {
-      const bool deferred = !(hx && hxm && hy && sFlag[tid - 32]);
+      deferred = !(hx && hxm && hy && sFlag[tid - 32]);
       if (!deferred) {
          HTR_UNROLL
          for (int e = 0; e < nEq; e++) {
             double v = ct[e];
             v += my*(Fy[e] - sF[e*NT + tid - 32]);
             v += mx*(Fx[e] - Fm[e]);
-            Ct[e] = v;
+            ct[e] = v;
          }
       }
       mask[maskIndex(c, tile)] = deferred;
       if (deferred) *flag = 1;
+   }
+   // rows of Conserved_t leave through shared memory as contiguous spans (deferred cells rewrite their old value)
+   if (f.Conserved_t.stride[0] == 8*nEq) {
+      __syncthreads();
+      double *sOut = d + j*(nEq*32);
+      if (upd) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) sOut[(i - 1)*nEq + e] = ct[e];
+      }
+      __syncwarp();
+      if (j >= 1 && c.y <= tile.hi[1]) {
+         Pt r0 = c; r0.x = cx0 + 1;
+         const int64_t left = tile.hi[0] - r0.x + 1;
+         const int nval = nEq*(int)(left < 31 ? left : 31);
+         double *row = at<double>(f.Conserved_t, r0);
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) { const int m = e*32 + i; if (m < nval) row[m] = sOut[m]; }
+      }
+   } else if (upd && !deferred) {
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) Ct[e] = ct[e];
    }
 }
 
