@@ -351,8 +351,15 @@ def run_gpu(args, rank, world, local_rank):
         kb = kernel_bytes(kind, nspec, scheme)
         ach = kb * cells_rank / (kern[top] * 1e-3) / 1e9
         B = algorithmic_bytes(nspec, scheme, diffusion, chemistry)
+        # measured DRAM bytes of that kernel (ncu --set full capture committed under profiles/), per launch
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "r1_dram_traffic.json")
+        if os.path.exists(tpath):
+            t = json.load(open(tpath)).get(cfg["type"], {}).get(top)
+            if t:
+                traffic = t["dram_bytes_per_cell"] * cells_rank
         roof = {"bound": "hbm", "kernel": top, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src, "kernel_ms": kern[top], "kernel_bytes_per_cell": kb,
+                "traffic": traffic, "peak_source": peak_src, "kernel_ms": kern[top], "kernel_bytes_per_cell": kb,
                 "kernels_ms": kern, "rhs_bytes_per_cell": B,
                 "rhs_achieved_gbs": B * cells_rank * world * args.steps / (ms * 1e-3) / 1e9 / world,
                 "rhs_frac": B * cells_rank * args.steps / (ms * 1e-3) / 1e9 / peak}
