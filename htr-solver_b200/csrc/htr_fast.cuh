@@ -146,9 +146,10 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
    const int i = threadIdx.x, k = threadIdx.y;
    const int tid = k*ZT_X + i;
    Pt c;
-   c.x = tile.lo[0] + (int64_t)blockIdx.x*ZT_X + i;
-   c.y = tile.lo[1] + blockIdx.y;
-   const int64_t cz0 = tile.lo[2] - 1 + (int64_t)blockIdx.z*(ZT_Z - 1);
+   // grid = (z blocks, x blocks, y): consecutive CTAs are z-neighbours, whose tiles share 6 of 21 planes in L2
+   c.x = tile.lo[0] + (int64_t)blockIdx.y*ZT_X + i;
+   c.y = tile.lo[1] + blockIdx.z;
+   const int64_t cz0 = tile.lo[2] - 1 + (int64_t)blockIdx.x*(ZT_Z - 1);
    c.z = cz0 + k;
    const bool inX = c.x <= tile.hi[0];
 
@@ -362,55 +363,60 @@ HTR_DEV double derivStd(double xm1, double x, double xp1, double m) {
 }
 HTR_DEV double interpStd(double x1, double x2) { return c_Interp[Std_node][0]*x1 + c_Interp[Std_node][1]*x2; }
 
-// Stages cell q (already wrapped) into slot idx; returns true if a node type the fast path does not handle
-// is involved.  JD = 1: derivatives G0..G6 = dUdX dVdX dUdY dVdY dUdZ dVdZ dWdZ;  JD = 2: dUdX dWdX dVdY dWdY.
+// Stages cell q (already wrapped) into slot idx, one PART of its data per call so that the (cell, part) items of
+// a tile spread evenly over the threads (a 33x9 box on 256 threads would otherwise leave 215 threads waiting at the
+// barrier for the 41 that stage a second cell).  Returns true if a node type the fast path does not handle is
+// involved.  Parts: 0 rho mu lam T Xi MixW | 1 Di rhoYi | 2 u, d/dx, d/dy | 3 d/dz (xy kernel only).
+// JD = 1: derivatives G0..G6 = dUdX dVdX dUdY dVdY dUdZ dVdZ dWdZ;  JD = 2: dUdX dWdX dVdY dWdY.
 template<int JD, int NC>
-HTR_DEV bool stageDiffCell(double *s, const int idx, const htr_fluid &f, const Pt &q, const htr_rect &B) {
+HTR_DEV bool stageDiffPart(const int part, double *s, const int idx, const htr_fluid &f, const Pt &q, const htr_rect &B) {
    using L = DLay<JD>;
-   s[L::O_RHO*NC + idx] = ld<double>(f.rho, q);
-   s[L::O_MU*NC + idx] = ld<double>(f.mu, q);
-   s[L::O_LAM*NC + idx] = ld<double>(f.lam, q);
-   s[L::O_T*NC + idx] = ld<double>(f.temperature, q);
-   double Xi[nSpec];
-   HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) {
-      Xi[i] = ldc<double>(f.MolarFracs, q, i);
-      s[(L::O_X + i)*NC + idx] = Xi[i];
-      s[(L::O_DI + i)*NC + idx] = ldc<double>(f.Di, q, i);
-      s[(L::O_RY + i)*NC + idx] = ldc<double>(f.Conserved, q, i);
-   }
-   s[L::O_MW*NC + idx] = mix::GetMolarWeightFromXi(Xi);
-   double u[3];
-   HTR_UNROLL
-   for (int i = 0; i < 3; i++) { u[i] = ldc<double>(f.velocity, q, i); s[(L::O_U + i)*NC + idx] = u[i]; }
-
    bool bad = false;
-   {  // d/dx
-      Pt a = q, b = q;
-      a.x = wrapCoord(q.x - 1, B.lo[0], B.hi[0]); b.x = wrapCoord(q.x + 1, B.lo[0], B.hi[0]);
-      bad = bad || (ld<int>(f.nType_x, q) != Std_node);
-      const double m = ld<double>(f.dcsi_d, q);
-      constexpr int c1 = (JD == 1) ? 1 : 2;       // second component needed: V (xy kernel) or W (z kernel)
-      s[(L::O_G + 0)*NC + idx] = derivStd(ldc<double>(f.velocity, a, 0), u[0], ldc<double>(f.velocity, b, 0), m);
-      s[(L::O_G + 1)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
-   }
-   {  // d/dy
-      Pt a = q, b = q;
-      a.y = wrapCoord(q.y - 1, B.lo[1], B.hi[1]); b.y = wrapCoord(q.y + 1, B.lo[1], B.hi[1]);
-      bad = bad || (ld<int>(f.nType_y, q) != Std_node);
-      const double m = ld<double>(f.deta_d, q);
-      constexpr int c0 = (JD == 1) ? 0 : 1, c1 = (JD == 1) ? 1 : 2;   // (U,V) or (V,W)
-      s[(L::O_G + 2)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c0), u[c0], ldc<double>(f.velocity, b, c0), m);
-      s[(L::O_G + 3)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
-   }
-   if (JD == 1) {  // d/dz
+   if (part == 0) {
+      s[L::O_RHO*NC + idx] = ld<double>(f.rho, q);
+      s[L::O_MU*NC + idx] = ld<double>(f.mu, q);
+      s[L::O_LAM*NC + idx] = ld<double>(f.lam, q);
+      s[L::O_T*NC + idx] = ld<double>(f.temperature, q);
+      double Xi[nSpec];
+      HTR_UNROLL
+      for (int i = 0; i < nSpec; i++) { Xi[i] = ldc<double>(f.MolarFracs, q, i); s[(L::O_X + i)*NC + idx] = Xi[i]; }
+      s[L::O_MW*NC + idx] = mix::GetMolarWeightFromXi(Xi);
+   } else if (part == 1) {
+      HTR_UNROLL
+      for (int i = 0; i < nSpec; i++) {
+         s[(L::O_DI + i)*NC + idx] = ldc<double>(f.Di, q, i);
+         s[(L::O_RY + i)*NC + idx] = ldc<double>(f.Conserved, q, i);
+      }
+   } else if (part == 2) {
+      double u[3];
+      HTR_UNROLL
+      for (int i = 0; i < 3; i++) { u[i] = ldc<double>(f.velocity, q, i); s[(L::O_U + i)*NC + idx] = u[i]; }
+      {  // d/dx
+         Pt a = q, b = q;
+         a.x = wrapCoord(q.x - 1, B.lo[0], B.hi[0]); b.x = wrapCoord(q.x + 1, B.lo[0], B.hi[0]);
+         bad = bad || (ld<int>(f.nType_x, q) != Std_node);
+         const double m = ld<double>(f.dcsi_d, q);
+         constexpr int c1 = (JD == 1) ? 1 : 2;       // second component needed: V (xy kernel) or W (z kernel)
+         s[(L::O_G + 0)*NC + idx] = derivStd(ldc<double>(f.velocity, a, 0), u[0], ldc<double>(f.velocity, b, 0), m);
+         s[(L::O_G + 1)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
+      }
+      {  // d/dy
+         Pt a = q, b = q;
+         a.y = wrapCoord(q.y - 1, B.lo[1], B.hi[1]); b.y = wrapCoord(q.y + 1, B.lo[1], B.hi[1]);
+         bad = bad || (ld<int>(f.nType_y, q) != Std_node);
+         const double m = ld<double>(f.deta_d, q);
+         constexpr int c0 = (JD == 1) ? 0 : 1, c1 = (JD == 1) ? 1 : 2;   // (U,V) or (V,W)
+         s[(L::O_G + 2)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c0), u[c0], ldc<double>(f.velocity, b, c0), m);
+         s[(L::O_G + 3)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
+      }
+   } else if (JD == 1) {  // d/dz
       Pt a = q, b = q;
       a.z = wrapCoord(q.z - 1, B.lo[2], B.hi[2]); b.z = wrapCoord(q.z + 1, B.lo[2], B.hi[2]);
       bad = bad || (ld<int>(f.nType_z, q) != Std_node);
       const double m = ld<double>(f.dzet_d, q);
       HTR_UNROLL
       for (int i = 0; i < 3; i++)
-         s[(L::O_G + 4 + i)*NC + idx] = derivStd(ldc<double>(f.velocity, a, i), u[i], ldc<double>(f.velocity, b, i), m);
+         s[(L::O_G + 4 + i)*NC + idx] = derivStd(ldc<double>(f.velocity, a, i), ldc<double>(f.velocity, q, i), ldc<double>(f.velocity, b, i), m);
    }
    return bad;
 }
@@ -521,7 +527,9 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
       if (DOX) mx = ld<double>(f.dcsi_d, c);
    }
    bool bad = false;
-   for (int n = tid; n < NC; n += NT) {
+   constexpr int NP = DOX ? 4 : 3;
+   for (int item = tid; item < NP*NC; item += NT) {
+      const int part = item/NC, n = item - part*NC;
       const int rr = n/W, cc = n - rr*W;
       const int64_t x = cx0 + cc, J = cJ0 + rr;
       if (x <= tile.hi[0] + 1 && J <= tile.hi[JD] + 1) {
@@ -529,7 +537,7 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
          q.x = wrapCoord(x, B.lo[0], B.hi[0]);
          (JD == 1 ? q.y : q.z) = wrapCoord(J, B.lo[JD], B.hi[JD]);
          (JD == 1 ? q.z : q.y) = cK;
-         bad = stageDiffCell<JD, NC>(s, n, f, q, B) || bad;
+         bad = stageDiffPart<JD, NC>(part, s, n, f, q, B) || bad;
       }
    }
 

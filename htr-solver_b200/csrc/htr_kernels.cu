@@ -211,7 +211,7 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
       attr = true;
    }
    if (parts & PART_EZ) {
-      dim3 grid((unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1], (unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)));
+      dim3 grid((unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)), (unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1]);
       dim3 block(fast::ZT_X, fast::ZT_Z, 1);
       if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
       else      fast::euler_z_chem_kernel<HY, false><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
