@@ -189,6 +189,18 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+_JSON_FD = None
+
+
+def emit(text):
+    """The one JSON line of this run, on the real stdout."""
+    if _JSON_FD is None:
+        print(text, flush=True)
+    else:
+        sys.stdout.flush()
+        os.write(_JSON_FD, (text + "\n").encode())
+
+
 def tiles_for(world):
     return {1: (1, 1, 1), 2: (1, 1, 2), 4: (1, 2, 2), 8: (2, 2, 2)}.get(world) or (1, 1, world)
 
@@ -385,7 +397,7 @@ def run_gpu(args, rank, world, local_rank):
                        "halo": "none (periodic wrap by index)" if world == 1 else "3 ghost planes, NCCL send/recv per step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
             "roofline": roof, "cpu_baseline": cpu, "build": solver.L.htr_build_info().decode()}
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
 def main():
@@ -409,6 +421,12 @@ def main():
         run_reference(args, rank, world)
         return
     if world > 1:
+        # stdout must carry exactly ONE JSON line: NCCL prints its version banner to fd 1 when the first communicator is
+        # created, so fd 1 points at stderr until the line is emitted through the saved descriptor
+        global _JSON_FD
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
         import torch
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

@@ -31,6 +31,39 @@ __device__ __forceinline__ Pt shift(const Pt &p, int off, const htr_rect &B) {
    return q;
 }
 
+// ---- tile-relative 32-bit addressing (staged kernels) -----------------------------------------
+// The staged kernels address cells relative to tile.lo with 32-bit coordinates and strides: one
+// IMAD.WIDE per term instead of a 64x64-bit multiply per term per field (the per-field byte strides made
+// 9-16 % of their instructions).  Built on the host by makeRelative() (htr_kernels.cu); a layout whose
+// strides do not fit 31 bits takes the per-task kernels.
+struct racc { char *base; int s[3]; };           // base = address of cell tile.lo
+struct rbox { int lo[3], hi[3]; };               // inclusive, relative to tile.lo, clamped to +-2^30
+struct RPt { int x, y, z; };
+struct rfluid {                                  // same members, same order as htr_fluid
+   racc nType_x, nType_y, nType_z;
+   racc dcsi_e, deta_e, dzet_e;
+   racc dcsi_d, deta_d, dzet_d;
+   racc dcsi_s, deta_s, dzet_s;
+   racc rho, mu, lam, Di, SoS;
+   racc pressure, temperature, MassFracs, MolarFracs, velocity;
+   racc Conserved, Conserved_old, Conserved_t, Conserved_t_old;
+   racc shockSensorX, shockSensorY, shockSensorZ;
+   racc DucrosSensor;
+};
+static_assert(sizeof(rfluid)/sizeof(racc) == sizeof(htr_fluid)/sizeof(htr_acc), "rfluid mirrors htr_fluid");
+
+template<typename T>
+__device__ __forceinline__ T *at(const racc &a, const RPt &p) {
+   return reinterpret_cast<T*>(a.base + (int64_t)p.x*a.s[0] + (int64_t)p.y*a.s[1] + (int64_t)p.z*a.s[2]);
+}
+template<typename T>
+__device__ __forceinline__ T ld(const racc &a, const RPt &p) { return __ldg(at<const T>(a, p)); }
+template<typename T>
+__device__ __forceinline__ T ldc(const racc &a, const RPt &p, int c) { return __ldg(at<const T>(a, p) + c); }
+
+template<int dir> __device__ __forceinline__ const racc &m_dOf(const rfluid &f)   { return dir == 0 ? f.dcsi_d : (dir == 1 ? f.deta_d : f.dzet_d); }
+template<int dir> __device__ __forceinline__ const racc &m_sOf(const rfluid &f)   { return dir == 0 ? f.dcsi_s : (dir == 1 ? f.deta_s : f.dzet_s); }
+
 template<int dir> __device__ __forceinline__ const htr_acc &nTypeOf(const htr_fluid &f) { return dir == 0 ? f.nType_x : (dir == 1 ? f.nType_y : f.nType_z); }
 template<int dir> __device__ __forceinline__ const htr_acc &m_eOf(const htr_fluid &f)   { return dir == 0 ? f.dcsi_e : (dir == 1 ? f.deta_e : f.dzet_e); }
 template<int dir> __device__ __forceinline__ const htr_acc &m_dOf(const htr_fluid &f)   { return dir == 0 ? f.dcsi_d : (dir == 1 ? f.deta_d : f.dzet_d); }

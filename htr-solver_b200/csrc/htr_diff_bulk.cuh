@@ -103,7 +103,7 @@ HTR_DEV void diffFaceRaw(double *Flux, const double *d, const int n, const int d
 
 template<int JD, int TJ>
 __global__ void __launch_bounds__(32*TJ, HTR_DB_MINB)
-diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag,
+diffusion_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__restrict__ mask, int *__restrict__ flag,
                       const int bulkOK) {
    using L = DB<JD, TJ>;
    constexpr bool DOX = L::DOX;
@@ -116,19 +116,19 @@ diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, 
 
    const int i = threadIdx.x, j = threadIdx.y;
    const int tid = j*32 + i;
-   const int64_t cx0 = DOX ? (tile.lo[0] - 1 + (int64_t)blockIdx.x*31) : (tile.lo[0] + (int64_t)blockIdx.x*32);
-   const int64_t cJ0 = tile.lo[JD] - 1 + (int64_t)blockIdx.y*(TJ - 1);
-   const int64_t cK = tile.lo[KD] + blockIdx.z;
-   const int64_t xs = (cx0 - 1) - (((cx0 - 1) + ((bulkOK >> 1) & 1)) & 1);
+   const int cx0 = DOX ? (tile.lo[0] - 1 + (int)blockIdx.x*31) : (tile.lo[0] + (int)blockIdx.x*32);
+   const int cJ0 = tile.lo[JD] - 1 + (int)blockIdx.y*(TJ - 1);
+   const int cK = tile.lo[KD] + blockIdx.z;
+   const int xs = (cx0 - 1) - (((cx0 - 1) + ((bulkOK >> 1) & 1)) & 1);
    const int co = (int)((cx0 - 1) - xs);
-   auto mk = [&](int64_t x, int64_t J, int64_t K) { Pt p; p.x = x; (JD == 1 ? p.y : p.z) = J; (JD == 1 ? p.z : p.y) = K; return p; };
-   const Pt c = mk(cx0 + i, cJ0 + j, cK);
-   const int64_t cJ = cJ0 + j;
+   auto mk = [&](int x, int J, int K) { RPt p; p.x = x; (JD == 1 ? p.y : p.z) = J; (JD == 1 ? p.z : p.y) = K; return p; };
+   const RPt c = mk(cx0 + i, cJ0 + j, cK);
+   const int cJ = cJ0 + j;
 
-   const int64_t xlo = (tile.lo[0] - 3 > B.lo[0]) ? tile.lo[0] - 3 : B.lo[0];
-   const int64_t xhi = (tile.hi[0] + 3 < B.hi[0]) ? tile.hi[0] + 3 : B.hi[0];
+   const int xlo = (tile.lo[0] - 3 > B.lo[0]) ? tile.lo[0] - 3 : B.lo[0];
+   const int xhi = (tile.hi[0] + 3 < B.hi[0]) ? tile.hi[0] + 3 : B.hi[0];
    const bool useBulk = (bulkOK & 1) && xs >= xlo && xs + W - 1 <= xhi;
-   const int64_t Km = wrapCoord(cK - 1, B.lo[KD], B.hi[KD]), Kp = wrapCoord(cK + 1, B.lo[KD], B.hi[KD]);
+   const int Km = wrapCoord(cK - 1, B.lo[KD], B.hi[KD]), Kp = wrapCoord(cK + 1, B.lo[KD], B.hi[KD]);
 
    if (tid == 0) bulk::mbarInit(bar, 1);
    __syncthreads();
@@ -151,14 +151,14 @@ diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, 
             if (item >= 10*ROWS) {                            // the two extra in-plane velocity rows (xy kernel)
                const int ru = (item == 10*ROWS) ? 0 : TJ + 2;
                if (!urowValid(ru)) continue;
-               const Pt q = mk(xs, wrapCoord(cJ0 + ru - 1, B.lo[JD], B.hi[JD]), cK);
+               const RPt q = mk(xs, wrapCoord(cJ0 + ru - 1, B.lo[JD], B.hi[JD]), cK);
                bulk::copyRow(d + L::O_U0 + 3*W*ru, at<const double>(f.velocity, q), 24u*W, bar);
                continue;
             }
             const int rr = item/10, fld = item - 10*rr;
             if (fld == 7 ? !urowValid(rr + 1) : !rowValid(rr)) continue;
-            const int64_t J = wrapCoord(cJ0 + rr, B.lo[JD], B.hi[JD]);
-            const Pt q = mk(xs, J, cK);
+            const int J = wrapCoord(cJ0 + rr, B.lo[JD], B.hi[JD]);
+            const RPt q = mk(xs, J, cK);
             switch (fld) {
             case 0: bulk::copyRow(d + L::O_R + rr*W, at<const double>(f.rho, q), 8u*W, bar); break;
             case 1: bulk::copyRow(d + L::O_R + NCB + rr*W, at<const double>(f.mu, q), 8u*W, bar); break;
@@ -178,10 +178,10 @@ diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, 
       for (int n = tid; n < W*L::UROWS; n += NT) {
          const int ru = n/W, cc = n - ru*W;
          const int rr = ru - 1;
-         const int64_t x = xs + cc, J = cJ0 + rr;
+         const int x = xs + cc, J = cJ0 + rr;
          if (x < tile.lo[0] - 3 || x > tile.hi[0] + 3 || J < tile.lo[JD] - 3 || J > tile.hi[JD] + 3) continue;
-         const int64_t xw = wrapCoord(x, B.lo[0], B.hi[0]), Jw = wrapCoord(J, B.lo[JD], B.hi[JD]);
-         const Pt q = mk(xw, Jw, cK);
+         const int xw = wrapCoord(x, B.lo[0], B.hi[0]), Jw = wrapCoord(J, B.lo[JD], B.hi[JD]);
+         const RPt q = mk(xw, Jw, cK);
          HTR_UNROLL
          for (int k = 0; k < 3; k++) d[L::O_U0 + 3*n + k] = ldc<double>(f.velocity, q, k);
          if (rr < 0 || rr > TJ) continue;
@@ -196,7 +196,7 @@ diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, 
             d[L::O_D + nSpec*m + k] = ldc<double>(f.Di, q, k);
             d[L::O_C + nEq*m + k] = ldc<double>(f.Conserved, q, k);
          }
-         const Pt qm = mk(xw, Jw, Km), qp = mk(xw, Jw, Kp);
+         const RPt qm = mk(xw, Jw, Km), qp = mk(xw, Jw, Kp);
          HTR_UNROLL
          for (int k = 0; k < 3; k++) { d[L::O_UM + 3*m + k] = ldc<double>(f.velocity, qm, k); d[L::O_UP + 3*m + k] = ldc<double>(f.velocity, qp, k); }
       }
@@ -213,10 +213,10 @@ diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, 
       md[k][0] = md[k][1] = md[k][2] = 0.0;
       if (n < NCB) {
          const int rr = n/W, cc = n - rr*W;
-         const int64_t x = xs + cc, J = cJ0 + rr;
+         const int x = xs + cc, J = cJ0 + rr;
          if (cc >= 1 && cc <= W - 2 && x >= tile.lo[0] - 1 && x <= tile.hi[0] + 1 && J <= tile.hi[JD] + 1) {
             mine[k] = true;
-            const Pt q = mk(wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(J, B.lo[JD], B.hi[JD]), cK);
+            const RPt q = mk(wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(J, B.lo[JD], B.hi[JD]), cK);
             md[k][0] = ld<double>(f.dcsi_d, q);
             md[k][1] = ld<double>(f.deta_d, q);
             bad = bad || (ld<int>(f.nType_x, q) != Std_node) || (ld<int>(f.nType_y, q) != Std_node);
@@ -226,7 +226,7 @@ diffusion_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, 
    }
    const bool inTile = c.x <= tile.hi[0] && cJ <= tile.hi[JD];
    const bool jAct = inTile && (!DOX || i >= 1), xAct = DOX && inTile && j >= 1;
-   const Pt qo = mk(wrapCoord(c.x, B.lo[0], B.hi[0]), wrapCoord(cJ, B.lo[JD], B.hi[JD]), cK);   // own cell, wrapped
+   const RPt qo = mk(wrapCoord(c.x, B.lo[0], B.hi[0]), wrapCoord(cJ, B.lo[JD], B.hi[JD]), cK);   // own cell, wrapped
    if (JD == 2 && jAct) bad = bad || (ld<int>(f.nType_z, qo) != Std_node);
    double msJ = 0.0, msx = 0.0;
    if (jAct) msJ = ld<double>(m_sOf<JD>(f), qo);

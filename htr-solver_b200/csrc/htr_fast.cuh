@@ -2,7 +2,7 @@
 // grid (the whole grid of a periodic box):
 //
 //   euler_z_chem_kernel   Conserved_t  = 0 + chemistry source + Euler-z   (one write, no read)
-//   euler_xy_kernel       Conserved_t += Euler-y; += Euler-x              (one read-modify-write)
+//   euler_xy_bulk_kernel  Conserved_t += Euler-y; += Euler-x              (one read-modify-write; htr_fast_bulk.cuh)
 //
 // i.e. the reference's accumulation order 0 -> +chem -> +Ez -> +Ey -> +Ex (src/prometeo.rg:502-578)
 // in two passes over Conserved_t instead of five.  The Euler flux is the 6th-order Kennedy-Gruber
@@ -59,16 +59,16 @@ namespace fast {
 constexpr int NV = nSpec + 6;                 // staged variables per cell
 enum { V_RHO = 0, V_P = 1, V_H = 2, V_U = 3, V_Y = 6 };
 
-HTR_DEV int64_t wrapCoord(int64_t c, int64_t lo, int64_t hi) {
+HTR_DEV int wrapCoord(int c, int lo, int hi) {
    if (c > hi || c < lo) {
-      const int64_t size = hi - lo + 1;
+      const int size = hi - lo + 1;
       c = ((c - lo) % size + size) % size + lo;
    }
    return c;
 }
 
 template<int NC>
-HTR_DEV void stageCell(double *s, const int idx, const htr_fluid &f, const Pt &q) {
+HTR_DEV void stageCell(double *s, const int idx, const rfluid &f, const RPt &q) {
    const double rho = ld<double>(f.rho, q);
    const double p = ld<double>(f.pressure, q);
    s[V_RHO*NC + idx] = rho;
@@ -122,9 +122,9 @@ HTR_DEV void kgStdFlux(double *Flux, const double *s, const int i0, const int st
    Flux[irU + dir] -= fl[nEq];
 }
 
-HTR_DEV int64_t maskIndex(const Pt &c, const htr_rect &tile) {
-   const int64_t nx = tile.hi[0] - tile.lo[0] + 1, ny = tile.hi[1] - tile.lo[1] + 1;
-   return ((c.z - tile.lo[2])*ny + (c.y - tile.lo[1]))*nx + (c.x - tile.lo[0]);
+HTR_DEV int64_t maskIndex(const RPt &c, const rbox &tile) {      // tile.lo = 0
+   const int64_t nx = tile.hi[0] + 1, ny = tile.hi[1] + 1;
+   return ((int64_t)c.z*ny + c.y)*nx + c.x;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -136,7 +136,7 @@ constexpr size_t ZT_SMEM = sizeof(double)*NV*ZT_NC + ZT_NC + ZT_NT;
 
 template<bool HYBRID, bool CHEM>
 __global__ void __launch_bounds__(ZT_NT, HTR_K1_MINB)
-euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
+euler_z_chem_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    extern __shared__ double smem[];
    double *s = smem;
    uint8_t *sSens = reinterpret_cast<uint8_t*>(smem + NV*ZT_NC);
@@ -145,18 +145,18 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
 
    const int i = threadIdx.x, k = threadIdx.y;
    const int tid = k*ZT_X + i;
-   Pt c;
+   RPt c;
    // grid = (z blocks, x blocks, y): consecutive CTAs are z-neighbours, whose tiles share 6 of 21 planes in L2
-   c.x = tile.lo[0] + (int64_t)blockIdx.y*ZT_X + i;
+   c.x = tile.lo[0] + (int)blockIdx.y*ZT_X + i;
    c.y = tile.lo[1] + blockIdx.z;
-   const int64_t cz0 = tile.lo[2] - 1 + (int64_t)blockIdx.x*(ZT_Z - 1);
+   const int cz0 = tile.lo[2] - 1 + (int)blockIdx.x*(ZT_Z - 1);
    c.z = cz0 + k;
    const bool inX = c.x <= tile.hi[0];
 
    for (int r = k; r < ZT_ROWS; r += ZT_Z) {
-      const int64_t z = cz0 - 2 + r;
+      const int z = cz0 - 2 + r;
       if (inX && z >= tile.lo[2] - 3 && z <= tile.hi[2] + 3) {
-         const Pt q = {c.x, c.y, wrapCoord(z, B.lo[2], B.hi[2])};
+         const RPt q = {c.x, c.y, wrapCoord(z, B.lo[2], B.hi[2])};
          stageCell<ZT_NC>(s, r*ZT_X + i, f, q);
          if (HYBRID) sSens[r*ZT_X + i] = ld<uint8_t>(f.shockSensorZ, q);
       }
@@ -166,7 +166,7 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
    bool bad = false;
    double mz = 0.0, Tc = 0.0;
    if (faceActive) {
-      const Pt q = {c.x, c.y, wrapCoord(c.z, B.lo[2], B.hi[2])};
+      const RPt q = {c.x, c.y, wrapCoord(c.z, B.lo[2], B.hi[2])};
       bad = ld<int>(f.nType_z, q) != Std_node;
       if (upd) { mz = ld<double>(f.dzet_e, c); if (CHEM) Tc = ld<double>(f.temperature, c); }
    }
@@ -210,7 +210,7 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
    }
    // Conserved_t rows leave through shared memory: a warp's 32 cells are nEq*32 consecutive doubles of the
    // field, written as full 256-byte spans instead of nEq stores of 8 bytes at a 8*nEq-byte stride
-   if (f.Conserved_t.stride[0] == 8*nEq) {
+   if (f.Conserved_t.s[0] == 8*nEq) {
       __syncthreads();                                  // every warp has read its neighbour's flux from sF
       double *sOut = smem + k*(nEq*ZT_X);
       if (upd) {
@@ -219,8 +219,8 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
       }
       __syncwarp();
       if (k >= 1 && c.z <= tile.hi[2]) {                // warp-uniform: this row is updated
-         Pt r0 = c; r0.x = c.x - i;
-         const int64_t left = tile.hi[0] - r0.x + 1;
+         RPt r0 = c; r0.x = c.x - i;
+         const int left = tile.hi[0] - r0.x + 1;
          const int nval = nEq*(int)(left < ZT_X ? left : ZT_X);
          double *row = at<double>(f.Conserved_t, r0);
          HTR_UNROLL
@@ -230,104 +230,6 @@ euler_z_chem_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, ui
       double *Ct = at<double>(f.Conserved_t, c);
       HTR_UNROLL
       for (int e = 0; e < nEq; e++) Ct[e] = base[e];
-   }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Conserved_t += Euler-y; Conserved_t += Euler-x
-// block = 32 (x) x TY (y) cells of one z plane; blocks overlap by one cell in x and y
-// ---------------------------------------------------------------------------------------------
-template<int TY> struct XYTile {
-   static constexpr int W = 37, ROWS = TY + 5, NC = W*ROWS, NT = 32*TY;
-   static constexpr size_t SMEM = sizeof(double)*NV*NC + 2*NC + NT;
-};
-
-template<int TY, bool HYBRID>
-__global__ void __launch_bounds__(32*TY, HTR_K2_MINB)
-euler_xy_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
-   using T = XYTile<TY>;
-   constexpr int W = T::W, NC = T::NC, NT = T::NT;
-   extern __shared__ double smem[];
-   double *s = smem;
-   uint8_t *sSensX = reinterpret_cast<uint8_t*>(smem + NV*NC);
-   uint8_t *sSensY = sSensX + NC;
-   uint8_t *sFlag = sSensY + NC;
-   static_assert(NV*NC >= nEq*NT, "flux exchange reuses the staging buffer");
-
-   const int i = threadIdx.x, j = threadIdx.y;
-   const int tid = j*32 + i;
-   const int64_t cx0 = tile.lo[0] - 1 + (int64_t)blockIdx.x*31;
-   const int64_t cy0 = tile.lo[1] - 1 + (int64_t)blockIdx.y*(TY - 1);
-   Pt c;
-   c.x = cx0 + i; c.y = cy0 + j; c.z = tile.lo[2] + blockIdx.z;
-
-   for (int n = tid; n < NC; n += NT) {
-      const int rr = n/W, cc = n - rr*W;
-      const int64_t x = cx0 - 2 + cc, y = cy0 - 2 + rr;
-      const bool need = ((rr >= 3 && rr <= TY + 1) || (cc >= 3 && cc <= 33)) &&
-                        x >= tile.lo[0] - 3 && x <= tile.hi[0] + 3 && y >= tile.lo[1] - 3 && y <= tile.hi[1] + 3;
-      if (need) {
-         const Pt q = {wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(y, B.lo[1], B.hi[1]), c.z};
-         stageCell<NC>(s, n, f, q);
-         if (HYBRID) {
-            sSensX[n] = ld<uint8_t>(f.shockSensorX, q);
-            sSensY[n] = ld<uint8_t>(f.shockSensorY, q);
-         }
-      }
-   }
-   const bool inTile = c.x <= tile.hi[0] && c.y <= tile.hi[1];
-   const bool xAct = inTile && j >= 1, yAct = inTile && i >= 1;
-   bool bad = false;
-   if (xAct || yAct) {
-      const Pt q = {wrapCoord(c.x, B.lo[0], B.hi[0]), wrapCoord(c.y, B.lo[1], B.hi[1]), c.z};
-      if (xAct) bad = ld<int>(f.nType_x, q) != Std_node;
-      if (yAct) bad = bad || (ld<int>(f.nType_y, q) != Std_node);
-   }
-   const bool anyBad = __syncthreads_or(bad);
-
-   const int own = (j + 2)*W + i + 2;
-   double Fx[nEq], Fy[nEq];
-   HTR_UNROLL
-   for (int e = 0; e < nEq; e++) { Fx[e] = 0.0; Fy[e] = 0.0; }
-   bool hx = false, hy = false;
-   if (!anyBad) {
-      if (yAct) {
-         hy = !HYBRID || (sSensY[own - W] && sSensY[own] && sSensY[own + W]);
-         if (hy) kgStdFlux<1, NC>(Fy, s, j*W + i + 2, W);
-      }
-      if (xAct) {
-         hx = !HYBRID || (sSensX[own - 1] && sSensX[own] && sSensX[own + 1]);
-         if (hx) kgStdFlux<0, NC>(Fx, s, (j + 2)*W + i, 1);
-      }
-   }
-   // minus x face: lane i-1 of the same warp (a warp is one row of the block)
-   double Fm[nEq];
-   HTR_UNROLL
-   for (int e = 0; e < nEq; e++) Fm[e] = __shfl_up_sync(0xffffffffu, Fx[e], 1);
-   const bool hxm = __shfl_up_sync(0xffffffffu, (int)hx, 1);
-   __syncthreads();
-   double *sF = smem;
-   if (hy) {
-      HTR_UNROLL
-      for (int e = 0; e < nEq; e++) sF[e*NT + tid] = Fy[e];
-   }
-   sFlag[tid] = hy;
-   __syncthreads();
-   if (inTile && i >= 1 && j >= 1) {
-      const bool deferred = !(hx && hxm && hy && sFlag[tid - 32]);
-      if (!deferred) {
-         double *Ct = at<double>(f.Conserved_t, c);
-         const double my = ld<double>(f.deta_e, c), mx = ld<double>(f.dcsi_e, c);
-         HTR_UNROLL
-         for (int e = 0; e < nEq; e++) {
-            double v = Ct[e];
-            v += my*(Fy[e] - sF[e*NT + tid - 32]);
-            v += mx*(Fx[e] - Fm[e]);
-            Ct[e] = v;
-         }
-      }
-      mask[maskIndex(c, tile)] = deferred;
-      if (deferred) *flag = 1;          // all writers store the same value
    }
 }
 
@@ -369,7 +271,7 @@ HTR_DEV double interpStd(double x1, double x2) { return c_Interp[Std_node][0]*x1
 // involved.  Parts: 0 rho mu lam T Xi MixW | 1 Di rhoYi | 2 u, d/dx, d/dy | 3 d/dz (xy kernel only).
 // JD = 1: derivatives G0..G6 = dUdX dVdX dUdY dVdY dUdZ dVdZ dWdZ;  JD = 2: dUdX dWdX dVdY dWdY.
 template<int JD, int NC>
-HTR_DEV bool stageDiffPart(const int part, double *s, const int idx, const htr_fluid &f, const Pt &q, const htr_rect &B) {
+HTR_DEV bool stageDiffPart(const int part, double *s, const int idx, const rfluid &f, const RPt &q, const rbox &B) {
    using L = DLay<JD>;
    bool bad = false;
    if (part == 0) {
@@ -392,7 +294,7 @@ HTR_DEV bool stageDiffPart(const int part, double *s, const int idx, const htr_f
       HTR_UNROLL
       for (int i = 0; i < 3; i++) { u[i] = ldc<double>(f.velocity, q, i); s[(L::O_U + i)*NC + idx] = u[i]; }
       {  // d/dx
-         Pt a = q, b = q;
+         RPt a = q, b = q;
          a.x = wrapCoord(q.x - 1, B.lo[0], B.hi[0]); b.x = wrapCoord(q.x + 1, B.lo[0], B.hi[0]);
          bad = bad || (ld<int>(f.nType_x, q) != Std_node);
          const double m = ld<double>(f.dcsi_d, q);
@@ -401,7 +303,7 @@ HTR_DEV bool stageDiffPart(const int part, double *s, const int idx, const htr_f
          s[(L::O_G + 1)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
       }
       {  // d/dy
-         Pt a = q, b = q;
+         RPt a = q, b = q;
          a.y = wrapCoord(q.y - 1, B.lo[1], B.hi[1]); b.y = wrapCoord(q.y + 1, B.lo[1], B.hi[1]);
          bad = bad || (ld<int>(f.nType_y, q) != Std_node);
          const double m = ld<double>(f.deta_d, q);
@@ -410,7 +312,7 @@ HTR_DEV bool stageDiffPart(const int part, double *s, const int idx, const htr_f
          s[(L::O_G + 3)*NC + idx] = derivStd(ldc<double>(f.velocity, a, c1), u[c1], ldc<double>(f.velocity, b, c1), m);
       }
    } else if (JD == 1) {  // d/dz
-      Pt a = q, b = q;
+      RPt a = q, b = q;
       a.z = wrapCoord(q.z - 1, B.lo[2], B.hi[2]); b.z = wrapCoord(q.z + 1, B.lo[2], B.hi[2]);
       bad = bad || (ld<int>(f.nType_z, q) != Std_node);
       const double m = ld<double>(f.dzet_d, q);
@@ -493,7 +395,7 @@ template<int JD, int TJ> struct DTile {
 
 template<int JD, int TJ>
 __global__ void __launch_bounds__(32*TJ, HTR_D_MINB)
-diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
+diffusion_staged_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
    using T = DTile<JD, TJ>;
    using L = DLay<JD>;
    constexpr bool DOX = T::DOX;
@@ -506,15 +408,15 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
 
    const int i = threadIdx.x, j = threadIdx.y;
    const int tid = j*32 + i;
-   const int64_t cx0 = DOX ? (tile.lo[0] - 1 + (int64_t)blockIdx.x*31) : (tile.lo[0] + (int64_t)blockIdx.x*32);
-   const int64_t cJ0 = tile.lo[JD] - 1 + (int64_t)blockIdx.y*(TJ - 1);
-   const int64_t cK = tile.lo[KD] + blockIdx.z;
-   Pt c;
+   const int cx0 = DOX ? (tile.lo[0] - 1 + (int)blockIdx.x*31) : (tile.lo[0] + (int)blockIdx.x*32);
+   const int cJ0 = tile.lo[JD] - 1 + (int)blockIdx.y*(TJ - 1);
+   const int cK = tile.lo[KD] + blockIdx.z;
+   RPt c;
    c.x = cx0 + i;
    (JD == 1 ? c.y : c.z) = cJ0 + j;
    (JD == 1 ? c.z : c.y) = cK;
 
-   const int64_t cJ = cJ0 + j;
+   const int cJ = cJ0 + j;
    const bool inTile = c.x <= tile.hi[0] && cJ <= tile.hi[JD];
    // own Conserved_t and metrics requested before the staging loop (latency hidden behind it)
    const bool upd = inTile && j >= 1 && (!DOX || i >= 1);
@@ -531,9 +433,9 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    for (int item = tid; item < NP*NC; item += NT) {
       const int part = item/NC, n = item - part*NC;
       const int rr = n/W, cc = n - rr*W;
-      const int64_t x = cx0 + cc, J = cJ0 + rr;
+      const int x = cx0 + cc, J = cJ0 + rr;
       if (x <= tile.hi[0] + 1 && J <= tile.hi[JD] + 1) {
-         Pt q;
+         RPt q;
          q.x = wrapCoord(x, B.lo[0], B.hi[0]);
          (JD == 1 ? q.y : q.z) = wrapCoord(J, B.lo[JD], B.hi[JD]);
          (JD == 1 ? q.z : q.y) = cK;
@@ -542,7 +444,7 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
    }
 
    const bool jAct = inTile && (!DOX || i >= 1), xAct = DOX && inTile && j >= 1;
-   Pt q = c;                                         // own cell, wrapped (it may be lo-1)
+   RPt q = c;                                         // own cell, wrapped (it may be lo-1)
    q.x = wrapCoord(c.x, B.lo[0], B.hi[0]);
    (JD == 1 ? q.y : q.z) = wrapCoord(cJ, B.lo[JD], B.hi[JD]);
    if (JD == 2 && jAct) bad = bad || (ld<int>(f.nType_z, q) != Std_node);
@@ -588,7 +490,7 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
       if (!ok) *flag = 1;
    }
    // rows of Conserved_t leave through shared memory as contiguous spans (a deferred tile rewrites its old values)
-   if (f.Conserved_t.stride[0] == 8*nEq) {
+   if (f.Conserved_t.s[0] == 8*nEq) {
       __syncthreads();
       double *sOut = smem + j*(nEq*32);
       constexpr int X0 = DOX ? 1 : 0, NXC = 32 - X0;      // first updated thread column, updated cells per row
@@ -598,8 +500,8 @@ diffusion_staged_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B
       }
       __syncwarp();
       if (j >= 1 && cJ <= tile.hi[JD]) {
-         Pt r0 = c; r0.x = cx0 + X0;
-         const int64_t left = tile.hi[0] - r0.x + 1;
+         RPt r0 = c; r0.x = cx0 + X0;
+         const int left = tile.hi[0] - r0.x + 1;
          const int nval = nEq*(int)(left < NXC ? left : NXC);
          double *row = at<double>(f.Conserved_t, r0);
          HTR_UNROLL

@@ -60,7 +60,7 @@ HTR_DEV void kgStdFluxRaw(double *Flux, const double *d, const int i0, const int
 
 template<int TY, bool HYBRID>
 __global__ void __launch_bounds__(32*TY, HTR_K2_MINB)
-euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, uint8_t *__restrict__ mask, int *__restrict__ flag,
+euler_xy_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__restrict__ mask, int *__restrict__ flag,
                      const int bulkOK) {
    using T = XYB<TY>;
    constexpr int W = T::W, NC = T::NC, NT = T::NT, ROWS = T::ROWS;
@@ -74,24 +74,24 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
 
    const int i = threadIdx.x, j = threadIdx.y;
    const int tid = j*32 + i;
-   const int64_t cx0 = tile.lo[0] - 1 + (int64_t)blockIdx.x*31;
-   const int64_t cy0 = tile.lo[1] - 1 + (int64_t)blockIdx.y*(TY - 1);
+   const int cx0 = tile.lo[0] - 1 + (int)blockIdx.x*31;
+   const int cy0 = tile.lo[1] - 1 + (int)blockIdx.y*(TY - 1);
    // first column of the tile: cx0-2 or cx0-3, whichever makes the row start 16-byte aligned
    // (bit 1 of bulkOK = parity of base/8, common to the copied fields)
-   const int64_t xs = (cx0 - 2) - (((cx0 - 2) + ((bulkOK >> 1) & 1)) & 1);
+   const int xs = (cx0 - 2) - (((cx0 - 2) + ((bulkOK >> 1) & 1)) & 1);
    const int co = (int)((cx0 - 2) - xs);                    // column of stencil offset -2 of thread i = 0
-   Pt c;
+   RPt c;
    c.x = cx0 + i; c.y = cy0 + j; c.z = tile.lo[2] + blockIdx.z;
 
    // can whole rows be copied?  (inside the allocation, not cut by the periodic wrap)
-   const int64_t xlo = (tile.lo[0] - 3 > B.lo[0]) ? tile.lo[0] - 3 : B.lo[0];
-   const int64_t xhi = (tile.hi[0] + 3 < B.hi[0]) ? tile.hi[0] + 3 : B.hi[0];
+   const int xlo = (tile.lo[0] - 3 > B.lo[0]) ? tile.lo[0] - 3 : B.lo[0];
+   const int xhi = (tile.hi[0] + 3 < B.hi[0]) ? tile.hi[0] + 3 : B.hi[0];
    const bool useBulk = (bulkOK & 1) && xs >= xlo && xs + W - 1 <= xhi;
 
    if (tid == 0) bulk::mbarInit(bar, 1);
    __syncthreads();
 
-   auto rowValid = [&](int rr) { const int64_t y = cy0 - 2 + rr; return y >= tile.lo[1] - 3 && y <= tile.hi[1] + 3; };
+   auto rowValid = [&](int rr) { const int y = cy0 - 2 + rr; return y >= tile.lo[1] - 3 && y <= tile.hi[1] + 3; };
    if (useBulk) {
       if (j == 0) {                                          // warp 0 issues the copies
          if (i == 0) {
@@ -103,7 +103,7 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
          for (int item = i; item < 4*ROWS; item += 32) {
             const int rr = item >> 2, fld = item & 3;
             if (!rowValid(rr)) continue;
-            const Pt q = {xs, wrapCoord(cy0 - 2 + rr, B.lo[1], B.hi[1]), c.z};
+            const RPt q = {xs, wrapCoord(cy0 - 2 + rr, B.lo[1], B.hi[1]), c.z};
             if (fld == 0)      bulk::copyRow(d + T::O_RHO + rr*W, at<const double>(f.rho, q), 8u*W, bar);
             else if (fld == 1) bulk::copyRow(d + T::O_P + rr*W, at<const double>(f.pressure, q), 8u*W, bar);
             else if (fld == 2) bulk::copyRow(d + T::O_U + 3*rr*W, at<const double>(f.velocity, q), 24u*W, bar);
@@ -114,9 +114,9 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
       // cooperative loads, one cell per thread and pass (edge tiles, unaligned layouts)
       for (int n = tid; n < NC; n += NT) {
          const int rr = n/W, cc = n - rr*W;
-         const int64_t x = xs + cc, y = cy0 - 2 + rr;
+         const int x = xs + cc, y = cy0 - 2 + rr;
          if (x >= tile.lo[0] - 3 && x <= tile.hi[0] + 3 && y >= tile.lo[1] - 3 && y <= tile.hi[1] + 3) {
-            const Pt q = {wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(y, B.lo[1], B.hi[1]), c.z};
+            const RPt q = {wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(y, B.lo[1], B.hi[1]), c.z};
             d[T::O_RHO + n] = ld<double>(f.rho, q);
             d[T::O_P + n] = ld<double>(f.pressure, q);
             HTR_UNROLL
@@ -136,12 +136,12 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
       rhoE[k] = 0.0;
       if (n < NC) {
          const int rr = n/W, cc = n - rr*W;
-         const int64_t x = xs + cc, y = cy0 - 2 + rr;
+         const int x = xs + cc, y = cy0 - 2 + rr;
          const int rc = cc - co;                             // column relative to stencil offset -2 of i = 0
          const bool need = ((rr >= 3 && rr <= TY + 1 && rc >= 0 && rc <= 36) || (rc >= 3 && rc <= 33)) &&
                            x >= tile.lo[0] - 3 && x <= tile.hi[0] + 3 && y >= tile.lo[1] - 3 && y <= tile.hi[1] + 3;
          if (need) {
-            const Pt q = {wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(y, B.lo[1], B.hi[1]), c.z};
+            const RPt q = {wrapCoord(x, B.lo[0], B.hi[0]), wrapCoord(y, B.lo[1], B.hi[1]), c.z};
             rhoE[k] = ldc<double>(f.Conserved, q, irE);
             if (HYBRID) {
                sSensX[n] = ld<uint8_t>(f.shockSensorX, q);
@@ -163,7 +163,7 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
    }
    bool bad = false;
    if (xAct || yAct) {
-      const Pt q = {wrapCoord(c.x, B.lo[0], B.hi[0]), wrapCoord(c.y, B.lo[1], B.hi[1]), c.z};
+      const RPt q = {wrapCoord(c.x, B.lo[0], B.hi[0]), wrapCoord(c.y, B.lo[1], B.hi[1]), c.z};
       if (xAct) bad = ld<int>(f.nType_x, q) != Std_node;
       if (yAct) bad = bad || (ld<int>(f.nType_y, q) != Std_node);
    }
@@ -219,7 +219,7 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
       if (deferred) *flag = 1;
    }
    // rows of Conserved_t leave through shared memory as contiguous spans (deferred cells rewrite their old value)
-   if (f.Conserved_t.stride[0] == 8*nEq) {
+   if (f.Conserved_t.s[0] == 8*nEq) {
       __syncthreads();
       double *sOut = d + j*(nEq*32);
       if (upd) {
@@ -228,8 +228,8 @@ euler_xy_bulk_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, u
       }
       __syncwarp();
       if (j >= 1 && c.y <= tile.hi[1]) {
-         Pt r0 = c; r0.x = cx0 + 1;
-         const int64_t left = tile.hi[0] - r0.x + 1;
+         RPt r0 = c; r0.x = cx0 + 1;
+         const int left = tile.hi[0] - r0.x + 1;
          const int nval = nEq*(int)(left < 31 ? left : 31);
          double *row = at<double>(f.Conserved_t, r0);
          HTR_UNROLL

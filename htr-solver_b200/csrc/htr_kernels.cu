@@ -59,6 +59,12 @@ HTR_DEV void eulerFace(double *Flux, const htr_fluid &f, const Pt &p, int t, con
 // KIND = FLUX_EULER (SCHEME selects the reconstruction) or FLUX_DIFFUSION
 // MASKED: only the cells flagged in `mask` (dense over the tile, see htr_fast.cuh) are updated and only
 // the faces they need are evaluated; a block without flagged cells returns at once.
+// dense index of global cell c in the tile's mask (same enumeration as fast::maskIndex on relative coordinates)
+HTR_DEV int64_t maskIndexG(const Pt &c, const htr_rect &tile) {
+   const int64_t nx = tile.hi[0] - tile.lo[0] + 1, ny = tile.hi[1] - tile.lo[1] + 1;
+   return ((c.z - tile.lo[2])*ny + (c.y - tile.lo[1]))*nx + (c.x - tile.lo[0]);
+}
+
 template<int dir, int KIND, int SCHEME, bool MASKED>
 HTR_DEV void fluxBlock(const unsigned bx, const unsigned by, const unsigned bz, const htr_fluid &f, const htr_rect &tile,
                        const htr_rect &B, const EulerParams &ep, const uint8_t *__restrict__ mask) {
@@ -82,11 +88,11 @@ HTR_DEV void fluxBlock(const unsigned bx, const unsigned by, const unsigned bz, 
       mine = false;
       bool next = false;
       if (active) {
-         if (cd >= tile.lo[dir]) mine = mask[fast::maskIndex(c, tile)] != 0;
+         if (cd >= tile.lo[dir]) mine = mask[maskIndexG(c, tile)] != 0;
          if (cd < tile.hi[dir]) {
             Pt n = c;
             ((dir == 0) ? n.x : ((dir == 1) ? n.y : n.z)) += 1;
-            next = mask[fast::maskIndex(n, tile)] != 0;
+            next = mask[maskIndexG(n, tile)] != 0;
          }
       }
       need = mine || next;
@@ -178,14 +184,39 @@ static bool g_bulk_diffusion = false;   // htr_set_option("bulk_diffusion", 1): 
 static bool g_no_pipe = false;          // htr_set_option("pipeline", 0): htr_host_rhs without the z-slab copy/compute overlap
 static bool g_no_bulk = false;          // htr_set_option("bulk", 0): cooperative loads instead of TMA bulk copies
 
+// Tile-relative view of the fields for the staged kernels (htr_access.cuh).  false: a stride or an extent does not
+// fit the 32-bit form -> the caller uses the per-task kernels.
+static bool makeRelative(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, rfluid &rf, rbox &rt, rbox &rb) {
+   const htr_acc *src = reinterpret_cast<const htr_acc*>(&f);
+   racc *dst = reinterpret_cast<racc*>(&rf);
+   const int64_t LIM = (int64_t)1 << 30;
+   for (int d = 0; d < 3; d++) {
+      const int64_t n = tile.hi[d] - tile.lo[d] + 1;
+      if (n >= LIM) return false;
+      rt.lo[d] = 0; rt.hi[d] = (int)(n - 1);
+      const int64_t lo = B.lo[d] - tile.lo[d], hi = B.hi[d] - tile.lo[d];
+      rb.lo[d] = (int)(lo < -LIM ? -LIM : (lo > LIM ? LIM : lo));
+      rb.hi[d] = (int)(hi < -LIM ? -LIM : (hi > LIM ? LIM : hi));
+   }
+   for (size_t k = 0; k < sizeof(htr_fluid)/sizeof(htr_acc); k++) {
+      const htr_acc &a = src[k];
+      for (int d = 0; d < 3; d++) {
+         if (a.stride[d] >= 2*LIM || a.stride[d] <= -2*LIM) return false;
+         dst[k].s[d] = (int)a.stride[d];
+      }
+      dst[k].base = a.base ? static_cast<char*>(a.base) + tile.lo[0]*a.stride[0] + tile.lo[1]*a.stride[1] + tile.lo[2]*a.stride[2] : nullptr;
+   }
+   return true;
+}
+
 // Can rows of these fields be moved by cp.async.bulk?  Returns 0 (no) or 1 | parity<<1 (htr_bulk.cuh).
-static int bulkEligible(std::initializer_list<std::pair<const htr_acc*, int>> fields) {
+static int bulkEligible(std::initializer_list<std::pair<const racc*, int>> fields) {
    if (g_no_bulk) return 0;
    int parity = -1;
    for (auto &fc : fields) {
-      const htr_acc &a = *fc.first;
+      const racc &a = *fc.first;
       const uintptr_t b = (uintptr_t)a.base;
-      if (a.stride[0] != 8*fc.second || (a.stride[1] & 15) || (a.stride[2] & 15) || (b & 7)) return 0;
+      if (a.s[0] != 8*fc.second || (a.s[1] & 15) || (a.s[2] & 15) || (b & 7)) return 0;
       const int p = (int)((b >> 3) & 1);
       if (parity < 0) parity = p; else if (p != parity) return 0;
    }
@@ -196,6 +227,7 @@ enum { PART_EZ = 1, PART_EXY = 2, PART_DZ = 4, PART_DXY = 8, PART_ALL = 15 };
 
 template<int SCHEME>
 static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
+                                   const rfluid &rf, const rbox &rt, const rbox &rb,
                                    const EulerParams &ep, uint8_t *scratch, cudaStream_t st, int parts = PART_ALL) {
    constexpr bool HY = (SCHEME == HTR_SCHEME_HYBRID);
    constexpr int TY = HTR_K2_TY;
@@ -213,8 +245,8 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    if (parts & PART_EZ) {
       dim3 grid((unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)), (unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1]);
       dim3 block(fast::ZT_X, fast::ZT_Z, 1);
-      if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
-      else      fast::euler_z_chem_kernel<HY, false><<<grid, block, fast::ZT_SMEM, st>>>(f, tile, B, maskZ, flags);
+      if (chem) fast::euler_z_chem_kernel<HY, true><<<grid, block, fast::ZT_SMEM, st>>>(rf, rt, rb, maskZ, flags);
+      else      fast::euler_z_chem_kernel<HY, false><<<grid, block, fast::ZT_SMEM, st>>>(rf, rt, rb, maskZ, flags);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
       if ((e = launchMasked<2, FLUX_EULER, SCHEME>(f, tile, B, ep, maskZ, flags, st)) != cudaSuccess) return e;
@@ -222,8 +254,8 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    if (parts & PART_EXY) {
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TY - 2)/(TY - 1)), (unsigned)n[2]);
       dim3 block(32, TY, 1);
-      const int bulkOK = bulkEligible({{&f.rho, 1}, {&f.pressure, 1}, {&f.velocity, 3}, {&f.MassFracs, nSpec}});
-      fast::euler_xy_bulk_kernel<TY, HY><<<grid, block, fast::XYB<TY>::SMEM, st>>>(f, tile, B, maskXY, flags + 1, bulkOK);
+      const int bulkOK = bulkEligible({{&rf.rho, 1}, {&rf.pressure, 1}, {&rf.velocity, 3}, {&rf.MassFracs, nSpec}});
+      fast::euler_xy_bulk_kernel<TY, HY><<<grid, block, fast::XYB<TY>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 1, bulkOK);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
@@ -234,7 +266,8 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
 
 // Conserved_t += diffusion z; += y; += x through the staged kernels + masked generic passes (same scratch,
 // after launchFastEuler has consumed it in stream order; flags [2], [3] were cleared there).
-static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, uint8_t *scratch, cudaStream_t st,
+static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
+                                       const rfluid &rf, const rbox &rt, const rbox &rb, uint8_t *scratch, cudaStream_t st,
                                        int parts = PART_ALL) {
    constexpr int TJ = HTR_D_TJ;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
@@ -259,28 +292,28 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       }
       dim3 gz((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
       if (parts & PART_DZ) {
-         fast::diffusion_staged_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(f, tile, B, maskZ, flags + 2);
+         fast::diffusion_staged_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(rf, rt, rb, maskZ, flags + 2);
          if ((e = cudaGetLastError()) != cudaSuccess) return e;
          if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
       }
       if (!(parts & PART_DXY)) return cudaSuccess;
       dim3 gxy((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
-      fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(f, tile, B, maskXY, flags + 3);
+      fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
       return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st);
    }
-   const int bulkOK = bulkEligible({{&f.rho, 1}, {&f.mu, 1}, {&f.lam, 1}, {&f.temperature, 1}, {&f.MolarFracs, nSpec},
-                                    {&f.Di, nSpec}, {&f.Conserved, nEq}, {&f.velocity, 3}});
+   const int bulkOK = bulkEligible({{&rf.rho, 1}, {&rf.mu, 1}, {&rf.lam, 1}, {&rf.temperature, 1}, {&rf.MolarFracs, nSpec},
+                                    {&rf.Di, nSpec}, {&rf.Conserved, nEq}, {&rf.velocity, 3}});
    if (parts & PART_DZ) {
       dim3 grid((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
-      fast::diffusion_bulk_kernel<2, TJ><<<grid, dim3(32, TJ, 1), fast::DB<2, TJ>::SMEM, st>>>(f, tile, B, maskZ, flags + 2, bulkOK);
+      fast::diffusion_bulk_kernel<2, TJ><<<grid, dim3(32, TJ, 1), fast::DB<2, TJ>::SMEM, st>>>(rf, rt, rb, maskZ, flags + 2, bulkOK);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
    }
    if (parts & PART_DXY) {
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
-      fast::diffusion_bulk_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DB<1, TJ>::SMEM, st>>>(f, tile, B, maskXY, flags + 3, bulkOK);
+      fast::diffusion_bulk_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DB<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3, bulkOK);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
       if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
@@ -763,16 +796,17 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
    // Reference task order (src/prometeo.rg:502-578): 0, +chem, +Euler z,y,x, +diffusion z,y,x.
    cudaStream_t st = (cudaStream_t)stream;
    if (scheme < 0 || scheme > HTR_SCHEME_SKEWSYMMETRIC) return HTR_EINVAL;
-   if ((scheme == HTR_SCHEME_HYBRID || scheme == HTR_SCHEME_SKEWSYMMETRIC) && !g_no_fast) {
+   rfluid rf; rbox rt, rb;
+   if ((scheme == HTR_SCHEME_HYBRID || scheme == HTR_SCHEME_SKEWSYMMETRIC) && !g_no_fast && makeRelative(*f, *tile, *bounds, rf, rt, rb)) {
       const int64_t cells = (tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
       uint8_t *scratch = (uint8_t*)scratchFor((size_t)(2*cells + 16), st);
       if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
       const EulerParams ep = {RK0, RK1, deltaTime};
       cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
-         ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st, parts)
-         : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, ep, scratch, st, parts);
+         ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts)
+         : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts);
       if (e != cudaSuccess) return cuerr(e);
-      if (diffusion && (e = launchFastDiffusion(*f, *tile, *bounds, scratch, st, parts)) != cudaSuccess) return cuerr(e);
+      if (diffusion && (e = launchFastDiffusion(*f, *tile, *bounds, rf, rt, rb, scratch, st, parts)) != cudaSuccess) return cuerr(e);
       return HTR_OK;
    }
    if (parts != PART_ALL) return HTR_EINVAL;      // the per-task sequence below is not split
