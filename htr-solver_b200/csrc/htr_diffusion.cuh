@@ -22,8 +22,13 @@ HTR_DEV void velocityDeriv(double *g, const htr_fluid &f, const Pt &q, const htr
       g[i] = getDeriv(t, ldc<double>(f.velocity, qm, i), ldc<double>(f.velocity, q, i), ldc<double>(f.velocity, qp, i), m);
 }
 
+// spanFirst: this is the plus face of the first cell of the task's span.  The reference carries the transverse
+// gradients from face to face (vGrad[0] <- vGrad[1], src/prometeo_rhs.inl:1211-1212) assuming the span's first
+// minus face lies one cell below; on a left-boundary node (offM1 = 0: L_S, L_C) that face is the cell's own plus
+// face, so the first plus face of the span is evaluated with the gradients of p+1 on both sides
+// (src/prometeo_rhs.inl:1249-1268).  Reproduced here so that boundary cells match the reference.
 template<int dir>
-HTR_DEV void diffusionFaceFlux(double *Flux, const htr_fluid &f, const Pt &p, const htr_rect &B) {
+HTR_DEV void diffusionFaceFlux(double *Flux, const htr_fluid &f, const Pt &p, const htr_rect &B, const bool spanFirst = false) {
    constexpr int D1 = T1(dir), D2 = T2(dir);
    const int t = ld<int>(nTypeOf<dir>(f), p);
    const double m_s = ld<double>(m_sOf<dir>(f), p);
@@ -32,6 +37,10 @@ HTR_DEV void diffusionFaceFlux(double *Flux, const htr_fluid &f, const Pt &p, co
    double g1[2][3], g2[2][3];     // transverse gradients at p and p+1
    velocityDeriv<D1>(g1[0], f, p, B);   velocityDeriv<D2>(g2[0], f, p, B);
    velocityDeriv<D1>(g1[1], f, pp1, B); velocityDeriv<D2>(g2[1], f, pp1, B);
+   if (spanFirst && offM1(t) == 0) {
+      HTR_UNROLL
+      for (int i = 0; i < 3; i++) { g1[0][i] = g1[1][i]; g2[0][i] = g2[1][i]; }
+   }
 
    double Xp[nSpec], Xq[nSpec];
    HTR_UNROLL

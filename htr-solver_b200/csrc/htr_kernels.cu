@@ -110,7 +110,7 @@ HTR_DEV void fluxBlock(const unsigned bx, const unsigned by, const unsigned bz, 
       const int t = ld<int>(nTypeOf<dir>(f), p);
       double Flux[nEq];
       if (KIND == FLUX_EULER) eulerFace<dir, SCHEME>(Flux, f, p, t, B, ep);
-      else                    diffusionFaceFlux<dir>(Flux, f, p, B);
+      else                    diffusionFaceFlux<dir>(Flux, f, p, B, fd != 0 && cd == tile.lo[dir]);
       HTR_UNROLL
       for (int i = 0; i < nEq; i++) sF[i][tid] = Flux[i];
    }

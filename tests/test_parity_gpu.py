@@ -289,3 +289,79 @@ def test_staged_rhs_on_sub_boxes_of_a_ghost_block(cfg, chem, kw):
         if all(x <= y for x, y in zip(a, b)):
             s.UpdateDerivatives(fb, "Hybrid", True, chem, (1.0, 0.0), 1e-3, tile=htr.Rect.make(a, b), bounds=nowrap)
     assert np.array_equal(fb.download(["Conserved_t"])["Conserved_t"], ref)
+
+
+def _bounded_node_types(f):
+    """Node types of a box that is bounded by collocated (NSCBC-like) boundaries in x and staggered (wall-like)
+    boundaries in y and periodic in z, assigned like InitializeOperators does (src/prometeo_metric.rg:225-262):
+    x: L_C Lp1_C Std .. Rm2_C Rm1_C R_C;  y: L_S Lp1_S Lp2_S Std .. Rm3_S Rm2_S Rm1_S R_S."""
+    Std, L_S, Lp1_S, Lp2_S, Rm3_S, Rm2_S, Rm1_S, R_S, L_C, Lp1_C, Rm2_C, Rm1_C, R_C = range(13)
+    f["nType_x"][...] = Std; f["nType_y"][...] = Std; f["nType_z"][...] = Std
+    f["nType_x"][:, :, 0] = L_C; f["nType_x"][:, :, 1] = Lp1_C
+    f["nType_x"][:, :, -3] = Rm2_C; f["nType_x"][:, :, -2] = Rm1_C; f["nType_x"][:, :, -1] = R_C
+    f["nType_y"][:, 0, :] = L_S; f["nType_y"][:, 1, :] = Lp1_S; f["nType_y"][:, 2, :] = Lp2_S
+    f["nType_y"][:, -4, :] = Rm3_S; f["nType_y"][:, -3, :] = Rm2_S; f["nType_y"][:, -2, :] = Rm1_S; f["nType_y"][:, -1, :] = R_S
+
+
+@pytest.mark.parametrize("cfg,chem,kw", [(CP, False, {"front": 0.3, "stretch": 0.2}),
+                                         (AIR, True, {"species_wave": 1.0, "front": 0.3, "stretch": 0.1})], ids=["constprop", "air"])
+@pytest.mark.parametrize("variant", ["", "strict"], ids=["prod", "strict"])
+def test_boundary_node_types(cfg, chem, kw, variant):
+    """All 13 node types (src/prometeo_metric_coeffs.cc:42-209): every per-task flux kernel, the sensors and the
+    full htr_rhs on a box with collocated boundaries in x and staggered boundaries in y against the oracle.
+    The staged kernels must defer the tiles that touch a boundary to the generic kernels (and only those).
+    Compared on the cells the reference's flux tasks own (p_{x,y,z}_divg: everything but the boundary nodes
+    themselves, where a one-sided flux of the outermost node is not defined and the reference's span code
+    produces NaN too)."""
+    inner = (slice(None), slice(1, -1), slice(1, -1))
+    o = oracle_for(cfg)
+    n = (70, 26, 12)
+    f = host_state(o, n, cfg, **kw)
+    _bounded_node_types(f)
+    _sensors(o, f)
+    s = htr.Solver(cfg, variant=variant)
+    fl = to_device(s, f)
+    tol = 1e-14 if variant else TOL_FLUX
+    s.UpdateDucrosSensor(fl, 1.0)
+    fl.upload(f, ["DucrosSensor"])
+    for d, nm in enumerate(["shockSensorX", "shockSensorY", "shockSensorZ"]):
+        s.UpdateShockSensor(fl, d)
+        assert int((fl.download([nm])[nm] != f[nm]).sum()) == 0, nm
+    rk = (0.75, 0.25); dt = 1e-3
+    for scheme in EULER_SCHEMES:
+        for d in range(3):
+            f["Conserved_t"][...] = 0.0
+            fl.t["Conserved_t"].zero_()
+            o.euler_flux(f, scheme, d, rk[0], rk[1], dt)
+            s.UpdateUsingEulerFlux(fl, scheme, d, rk, dt)
+            e = scaled_err(fl.download(["Conserved_t"])["Conserved_t"][inner], f["Conserved_t"][inner], euler_scale(f, d))
+            assert e <= tol, (scheme, d, e)
+    for d in range(3):
+        f["Conserved_t"][...] = 0.0
+        fl.t["Conserved_t"].zero_()
+        o.diffusion_flux(f, d)
+        s.UpdateUsingDiffusionFlux(fl, d)
+        e = rel_err(fl.download(["Conserved_t"])["Conserved_t"][inner], f["Conserved_t"][inner])
+        assert e <= TOL_FLUX, ("diffusion", d, e)
+    for scheme in ("Hybrid", "SkewSymmetric"):
+        o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=rk[0], RK1=rk[1], dt=dt)
+        fl.t["Conserved_t"].fill_(5.0)
+        s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=rk, deltaTime=dt)
+        got = fl.download(["Conserved_t"])["Conserved_t"]
+        scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
+        if chem:
+            ref = f["Conserved_t"].copy()
+            f["Conserved_t"][...] = 0.0
+            o.add_chemistry_sources(f)
+            scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
+            f["Conserved_t"][...] = ref
+        e = scaled_err(got[inner], f["Conserved_t"][inner], scale)
+        assert e <= (TOL_CHEM if chem else TOL_FLUX), (scheme, e)
+        if variant == "strict":       # staged + deferred cells == per-task sequence, bit for bit
+            try:
+                s.set_option("fast", 0)
+                fl.t["Conserved_t"].fill_(5.0)
+                s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=rk, deltaTime=dt)
+            finally:
+                s.set_option("fast", 1)
+            assert np.array_equal(got[inner], fl.download(["Conserved_t"])["Conserved_t"][inner])
