@@ -103,6 +103,11 @@ def load_library(mix, variant=""):
     L.htr_update_properties_from_primitive.argtypes = [vp, vp, vp]
     L.htr_update_conserved_from_primitive.argtypes = [vp, vp, vp]
     L.htr_max_spectral_radius.argtypes = [vp, vp, vp, vp]
+    L.htr_rk_initialize_temporaries.argtypes = [vp, vp, vp]
+    L.htr_rk_initialize_time_derivatives.argtypes = [vp, vp, i, vp]
+    L.htr_rk_update_vars.argtypes = [i, d, i, vp, vp, vp]
+    L.htr_rk_stage.argtypes = [i, d, i, vp, vp, vp]
+    L.htr_time_step.argtypes = [i, i, i, d, vp, vp, vp, d, vp]
     L.htr_rhs.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_rhs_parts.argtypes = [i, i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
@@ -271,6 +276,35 @@ class Solver:
     def UpdateConservedFromPrimitive(self, fl, tile=None):
         t, _ = self._rects(fl, tile, None)
         self._check(self.L.htr_update_conserved_from_primitive(C.byref(fl.struct()), t, self._stream()), "htr_update_conserved_from_primitive")
+
+    # src/prometeo_rk.rg:46-111
+    def InitializeTemporaries(self, fl, tile=None):
+        t, _ = self._rects(fl, tile, None)
+        self._check(self.L.htr_rk_initialize_temporaries(C.byref(fl.struct()), t, self._stream()), "htr_rk_initialize_temporaries")
+
+    def InitializeTimeDerivatives(self, fl, implicitChemistry=False, tile=None):
+        t, _ = self._rects(fl, tile, None)
+        self._check(self.L.htr_rk_initialize_time_derivatives(C.byref(fl.struct()), t, int(implicitChemistry), self._stream()),
+                    "htr_rk_initialize_time_derivatives")
+
+    def UpdateVars(self, fl, stage, Integrator_deltaTime, implicitChemistry=False, tile=None):
+        t, _ = self._rects(fl, tile, None)
+        self._check(self.L.htr_rk_update_vars(int(stage), float(Integrator_deltaTime), int(implicitChemistry),
+                                              C.byref(fl.struct()), t, self._stream()), "htr_rk_update_vars")
+
+    def UpdateVarsAndRecover(self, fl, stage, Integrator_deltaTime, implicitChemistry=False, tile=None):
+        """UpdateVars(STAGE) + UpdatePrimitiveFromConserved + UpdatePropertiesFromPrimitive in one pass
+        (src/prometeo.rg:1427, :452, :470)."""
+        t, _ = self._rects(fl, tile, None)
+        self._check(self.L.htr_rk_stage(int(stage), float(Integrator_deltaTime), int(implicitChemistry),
+                                        C.byref(fl.struct()), t, self._stream()), "htr_rk_stage")
+
+    def TimeStep(self, fl, scheme, Integrator_deltaTime, diffusion=True, chemistry=False, vorticityScale=1.0,
+                 tile=None, bounds=None):
+        """One RK3 step of a block without boundary nodes (MainLoopBody, src/prometeo.rg:1348-1470)."""
+        t, b = self._rects(fl, tile, bounds)
+        self._check(self.L.htr_time_step(SCHEMES[scheme], int(diffusion), int(chemistry), float(vorticityScale),
+                                         C.byref(fl.struct()), t, b, float(Integrator_deltaTime), self._stream()), "htr_time_step")
 
     def CalculateMaxSpectralRadius(self, fl, tile=None, sync=True):
         t, _ = self._rects(fl, tile, None)

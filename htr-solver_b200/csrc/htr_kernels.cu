@@ -389,12 +389,9 @@ __global__ void __launch_bounds__(128) primitive_from_conserved_kernel(const htr
    *at<double>(f.pressure, p) = P;
 }
 
-__global__ void __launch_bounds__(128) properties_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
-   Pt p; if (!cellOf(p, tile)) return;
-   double Xi[nSpec], Yi[nSpec], Di[nSpec];
-   HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) Xi[i] = ldc<double>(f.MolarFracs, p, i);
-   const double P = ld<double>(f.pressure, p), T = ld<double>(f.temperature, p);
+// rho, mu, lam, Di, SoS, MassFracs of one cell from (Xi, P, T) (src/prometeo_variables.hpp:62-89)
+__device__ __forceinline__ void storeProperties(const htr_fluid &f, const Pt &p, const double *Xi, const double P, const double T) {
+   double Yi[nSpec], Di[nSpec];
    const double MixW = mix::GetMolarWeightFromXi(Xi);
    *at<double>(f.rho, p) = mix::GetRho(P, T, MixW);
    *at<double>(f.mu, p) = mix::GetViscosity(T, Xi);
@@ -406,6 +403,70 @@ __global__ void __launch_bounds__(128) properties_from_primitive_kernel(const ht
    double *oD = at<double>(f.Di, p), *oY = at<double>(f.MassFracs, p);
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) { oD[i] = Di[i]; oY[i] = Yi[i]; }
+}
+
+// ---- Runge-Kutta glue (src/prometeo_rk.rg:46-111, coefficients src/prometeo_const.rg:54-58) -------------
+__constant__ double c_rk[3][3] = {{1.0, 0.0, 1.0}, {3.0/4.0, 1.0/4.0, 1.0/4.0}, {1.0/3.0, 2.0/3.0, 2.0/3.0}};
+
+__global__ void __launch_bounds__(128) rk_initialize_temporaries_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   const double *C = at<const double>(f.Conserved, p);
+   double *Co = at<double>(f.Conserved_old, p);
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) Co[i] = C[i];
+}
+
+__global__ void __launch_bounds__(128) rk_initialize_time_derivatives_kernel(const htr_fluid f, const htr_rect tile, const int implicitChemistry) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double *Ct = at<double>(f.Conserved_t, p);
+   if (implicitChemistry) {
+      const double *Cto = at<const double>(f.Conserved_t_old, p);
+      HTR_UNROLL
+      for (int i = 0; i < nEq; i++) Ct[i] = -Cto[i];
+   } else {
+      HTR_UNROLL
+      for (int i = 0; i < nEq; i++) Ct[i] = 0.0;
+   }
+}
+
+// UpdateVars(STAGE); with RECOVER also UpdatePrimitiveFromConserved and UpdatePropertiesFromPrimitive of the
+// same cell from the registers (the three tasks the reference launches back to back after every stage,
+// src/prometeo.rg:1427, :452, :470).  The operation order of each task is kept, so the fused pass writes the
+// same bits as the three kernels in sequence.
+template<bool RECOVER>
+__global__ void __launch_bounds__(128) rk_update_vars_kernel(const htr_fluid f, const htr_rect tile, const int stage, const double dt) {
+   Pt p; if (!cellOf(p, tile)) return;
+   const double c1 = c_rk[stage][0], c2 = c_rk[stage][1], c3 = c_rk[stage][2];
+   const double *Co = at<const double>(f.Conserved_old, p), *Ct = at<const double>(f.Conserved_t, p);
+   double *C = at<double>(f.Conserved, p);
+   double U[nEq];
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) U[i] = (c1*Co[i] + c2*C[i]) + (c3*Ct[i])*dt;
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) C[i] = U[i];
+   if (RECOVER) {
+      double rho, Yi[nSpec], MixW, u[3], P, Xi[nSpec];
+      double T = *at<double>(f.temperature, p);
+      primitivesFromConserved(U, rho, Yi, MixW, u, T, P);
+      mix::GetMolarFractions(Xi, MixW, Yi);
+      double *X = at<double>(f.MolarFracs, p), *v = at<double>(f.velocity, p);
+      HTR_UNROLL
+      for (int i = 0; i < nSpec; i++) X[i] = Xi[i];
+      HTR_UNROLL
+      for (int i = 0; i < 3; i++) v[i] = u[i];
+      *at<double>(f.temperature, p) = T;
+      *at<double>(f.pressure, p) = P;
+      storeProperties(f, p, Xi, P, T);
+   }
+}
+
+__global__ void __launch_bounds__(128) properties_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double Xi[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Xi[i] = ldc<double>(f.MolarFracs, p, i);
+   const double P = ld<double>(f.pressure, p), T = ld<double>(f.temperature, p);
+   storeProperties(f, p, Xi, P, T);
 }
 
 __global__ void __launch_bounds__(128) conserved_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
@@ -766,6 +827,30 @@ int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *til
    properties_from_primitive_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
    return cuerr(cudaGetLastError());
 }
+int htr_rk_initialize_temporaries(const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   rk_initialize_temporaries_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   return cuerr(cudaGetLastError());
+}
+int htr_rk_initialize_time_derivatives(const htr_fluid *f, const htr_rect *tile, int implicitChemistry, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   rk_initialize_time_derivatives_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, implicitChemistry);
+   return cuerr(cudaGetLastError());
+}
+static int rkUpdate(bool recover, int stage, double dt, int implicitChemistry, const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (stage < 1 || stage > 3) return HTR_EINVAL;
+   if (implicitChemistry) dt *= 0.5;
+   if (recover) rk_update_vars_kernel<true><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
+   else rk_update_vars_kernel<false><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
+   return cuerr(cudaGetLastError());
+}
+int htr_rk_update_vars(int stage, double Integrator_deltaTime, int implicitChemistry, const htr_fluid *f, const htr_rect *tile, void *stream) {
+   return rkUpdate(false, stage, Integrator_deltaTime, implicitChemistry, f, tile, stream);
+}
+int htr_rk_stage(int stage, double Integrator_deltaTime, int implicitChemistry, const htr_fluid *f, const htr_rect *tile, void *stream) {
+   return rkUpdate(true, stage, Integrator_deltaTime, implicitChemistry, f, tile, stream);
+}
 int htr_update_conserved_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream) {
    HTR_CHECK_COMMON(f, tile)
    conserved_from_primitive_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
@@ -823,6 +908,29 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
       for (int d = 2; d >= 0; d--)
          if ((rc = htr_diffusion_flux(d, f, tile, bounds, stream)) != HTR_OK) return rc;
    return rc;
+}
+
+// ---- one RK3 time step of a block without boundary nodes (src/prometeo.rg:1348-1470, explicit chemistry) ---------
+// shock sensors once (Hybrid only, src/prometeo_sensor.rg:104-122), InitializeTemporaries, then per stage
+// UpdateDerivatives(RK_C[STAGE][1..2], dt*RK_C[STAGE][3]) and UpdateVars + primitive + property recovery.
+int htr_time_step(int scheme, int diffusion, int chemistry, double vorticityScale, const htr_fluid *f,
+                  const htr_rect *tile, const htr_rect *bounds, double Integrator_deltaTime, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds) return HTR_EINVAL;
+   static const double RK_C[3][3] = {{1.0, 0.0, 1.0}, {3.0/4.0, 1.0/4.0, 1.0/4.0}, {1.0/3.0, 2.0/3.0, 2.0/3.0}};
+   int rc;
+   if (scheme == HTR_SCHEME_HYBRID) {
+      if ((rc = htr_ducros_sensor(f, tile, bounds, vorticityScale, stream)) != HTR_OK) return rc;
+      for (int d = 0; d < 3; d++)
+         if ((rc = htr_shock_sensor(d, f, tile, bounds, stream)) != HTR_OK) return rc;
+   }
+   if ((rc = htr_rk_initialize_temporaries(f, tile, stream)) != HTR_OK) return rc;
+   for (int stage = 1; stage <= 3; stage++) {
+      const double *c = RK_C[stage - 1];
+      if ((rc = htr_rhs(scheme, diffusion, chemistry, f, tile, bounds, c[0], c[1], Integrator_deltaTime*c[2], stream)) != HTR_OK) return rc;
+      if ((rc = htr_rk_stage(stage, Integrator_deltaTime, 0, f, tile, stream)) != HTR_OK) return rc;
+   }
+   return HTR_OK;
 }
 
 // ---- host-buffer entry point (what a host-resident caller binds) ------------------------------

@@ -106,6 +106,23 @@ int htr_chemistry_failures(void);
 int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream);
 int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream);
 int htr_update_conserved_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream);
+/* Runge-Kutta glue (src/prometeo_rk.rg; the reference has Regent tasks only, no C++ task to swap, so an
+ * adapter registers these as new leaf tasks - INTEGRATION.md section 6).
+ *   htr_rk_initialize_temporaries       InitializeTemporaries, :46-56      Conserved_old = Conserved
+ *   htr_rk_initialize_time_derivatives  mkInitializeTimeDerivatives, :58-86  Conserved_t = 0, or -Conserved_t_old
+ *                                       with implicit chemistry
+ *   htr_rk_update_vars                  mkUpdateVars(STAGE), :88-111; stage = 1..3, coefficients RK_C
+ *                                       (src/prometeo_const.rg:54-58); dt is halved with implicit chemistry
+ *   htr_rk_stage                        UpdateVars(STAGE) + UpdatePrimitiveFromConserved +
+ *                                       UpdatePropertiesFromPrimitive in one pass over the tile (the three
+ *                                       launches of src/prometeo.rg:1427, :452, :470 when the tile has no
+ *                                       boundary nodes); same bits as the three calls in sequence */
+int htr_rk_initialize_temporaries(const htr_fluid *f, const htr_rect *tile, void *stream);
+int htr_rk_initialize_time_derivatives(const htr_fluid *f, const htr_rect *tile, int implicitChemistry, void *stream);
+int htr_rk_update_vars(int stage, double Integrator_deltaTime, int implicitChemistry, const htr_fluid *f,
+                       const htr_rect *tile, void *stream);
+int htr_rk_stage(int stage, double Integrator_deltaTime, int implicitChemistry, const htr_fluid *f,
+                 const htr_rect *tile, void *stream);
 /* CalculateMaxSpectralRadiusTask (src/prometeo_cfl.cc:36-93): the tile maximum is written to
  * *d_result (device double, the DeferredValue of the GPU variant, src/prometeo_cfl.hpp:181-189). */
 int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_result, void *stream);
@@ -121,6 +138,13 @@ int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const 
  * 8 += diffusion y, x.  15 = htr_rhs.  Hybrid and SkewSymmetric schemes with the "fast" option on. */
 int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
                   const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+/* One RK3 time step of a block without boundary nodes, explicit chemistry (MainLoopBody, src/prometeo.rg:1348-1470):
+ * UpdateShockSensors (Hybrid only), InitializeTemporaries, then for STAGE = 1..3 htr_rhs with
+ * RK_coeffs = RK_C[STAGE][1..2] and deltaTime*RK_C[STAGE][3] followed by htr_rk_stage.  The halo of `f`
+ * (periodic wrap inside `bounds`, or ghost planes filled by the caller) must be valid for every stage: with
+ * tile == bounds (one periodic block) nothing else is needed. */
+int htr_time_step(int scheme, int diffusion, int chemistry, double vorticityScale, const htr_fluid *f,
+                  const htr_rect *tile, const htr_rect *bounds, double Integrator_deltaTime, void *stream);
 
 /* ---- host-buffer stage (the call a host-resident driver binds) ----
  * h_* are HOST pointers (pinned for full copy bandwidth), dense [z][y][x][comp] over `tile`.

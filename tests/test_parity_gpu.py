@@ -365,3 +365,102 @@ def test_boundary_node_types(cfg, chem, kw, variant):
             finally:
                 s.set_option("fast", 1)
             assert np.array_equal(got[inner], fl.download(["Conserved_t"])["Conserved_t"][inner])
+
+
+RK_C = ((1.0, 0.0, 1.0), (3.0/4.0, 1.0/4.0, 1.0/4.0), (1.0/3.0, 2.0/3.0, 2.0/3.0))   # src/prometeo_const.rg:54-58
+
+
+@pytest.mark.parametrize("cfg,kw", [(CP, {}), (AIR, {"species_wave": 1.0, "T0": 4.0})], ids=["constprop", "air"])
+@pytest.mark.parametrize("implicit", [False, True], ids=["explicit", "implicit-chem"])
+def test_rk_glue(cfg, kw, implicit):
+    """InitializeTemporaries / InitializeTimeDerivatives / UpdateVars(STAGE) (src/prometeo_rk.rg:46-111, Regent only:
+    restated here in numpy, same expression order) and the fused UpdateVars + primitive + property recovery against
+    the oracle's UpdatePrimitiveFromConserved / UpdatePropertiesFromPrimitive tasks run on the numpy update."""
+    o = oracle_for(cfg)
+    f = host_state(o, (20, 14, 10), cfg, **kw)
+    rng = np.random.default_rng(5)
+    dt = 2.0e-4
+    for variant in ("", "strict"):
+        s = htr.Solver(cfg, variant=variant)
+        fl = to_device(s, f)
+        s.InitializeTemporaries(fl)
+        assert np.array_equal(fl.download(["Conserved_old"])["Conserved_old"], f["Conserved"])
+        h = {k: v.copy() for k, v in f.items()}
+        h["Conserved_old"] = h["Conserved"].copy()
+        h["Conserved_t_old"] = 0.01*h["Conserved"]*rng.standard_normal(h["Conserved"].shape)
+        fl.upload(h, ["Conserved_t_old"])
+        s.InitializeTimeDerivatives(fl, implicit)
+        want = -h["Conserved_t_old"] if implicit else np.zeros_like(h["Conserved"])
+        assert np.array_equal(fl.download(["Conserved_t"])["Conserved_t"], want)
+        for stage in (1, 2, 3):
+            # a perturbation of a few percent stands for the stage's RHS
+            h["Conserved_t"] = (20.0*h["Conserved"]*rng.standard_normal(h["Conserved"].shape)).copy()
+            fl.upload(h, ["Conserved_t"])
+            c1, c2, c3 = RK_C[stage - 1]
+            d = dt*0.5 if implicit else dt
+            h["Conserved"] = (c1*h["Conserved_old"] + c2*h["Conserved"]) + (c3*h["Conserved_t"])*d
+            # unfused: UpdateVars alone, bit-exact without FMA contraction
+            before = {k: fl.t[k].clone() for k in ("Conserved", "temperature")}
+            s.UpdateVars(fl, stage, dt, implicit)
+            got = fl.download(["Conserved"])["Conserved"]
+            if variant == "strict":
+                assert np.array_equal(got, h["Conserved"]), stage
+            assert rel_err(got, h["Conserved"]) <= 1e-15, stage
+            s.UpdatePrimitiveFromConserved(fl)
+            s.UpdatePropertiesFromPrimitive(fl)
+            names = ["Conserved", "temperature", "pressure", "velocity", "MolarFracs", "rho", "mu", "lam", "Di", "SoS", "MassFracs"]
+            seq = fl.download(names)
+            # fused: same bits as the three launches
+            for k, v in before.items():
+                fl.t[k].copy_(v)
+            s.UpdateVarsAndRecover(fl, stage, dt, implicit)
+            fused = fl.download(names)
+            for k in names:
+                assert np.array_equal(fused[k], seq[k]), (variant, stage, k)
+            # against the reference tasks on the numpy update
+            o.update_primitive_from_conserved(h)
+            o.update_properties_from_primitive(h)
+            for k in names:
+                assert rel_err(fused[k], h[k]) <= TOL_CHEM, (variant, stage, k, rel_err(fused[k], h[k]))
+            # carry the device state forward on the host so the stages chain on identical inputs
+            for k in names:
+                h[k] = fused[k].copy()
+    with pytest.raises(Exception):
+        s.UpdateVars(fl, 4, dt)
+
+
+@pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "Hybrid", False, {"front": 0.3}), (CP, "SkewSymmetric", False, {}),
+                                                (AIR, "Hybrid", True, {"species_wave": 1.0, "front": 0.2, "p0": 1.0, "T0": 6.0, "U": 0.5})],
+                         ids=["constprop-hybrid", "constprop-skew", "air-hybrid-chem"])
+def test_time_step(cfg, scheme, chem, kw):
+    """Two RK3 time steps through htr_time_step against the same task chain of the reference
+    (MainLoopBody, src/prometeo.rg:1348-1470): sensors, then per stage UpdateDerivatives, UpdateVars (numpy),
+    UpdatePrimitiveFromConserved, UpdatePropertiesFromPrimitive."""
+    o = oracle_for(cfg)
+    f = host_state(o, (24, 20, 16), cfg, **kw)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    dt = 0.4/o.max_spectral_radius(f)
+    if chem:   # explicit chemistry: stay inside the fastest species' time scale as well
+        f["Conserved_t"][...] = 0.0
+        o.add_chemistry_sources(f)
+        w = np.abs(f["Conserved_t"][..., :o.nspec]).max(axis=-1)
+        dt = min(dt, 0.005*float((f["rho"]/w).min()))
+    names = ["Conserved", "temperature", "pressure", "velocity", "MolarFracs", "rho", "mu", "lam", "Di", "SoS", "MassFracs"]
+    for step in range(2):
+        if scheme == "Hybrid":
+            _sensors(o, f, 1.0)
+        f["Conserved_old"] = f["Conserved"].copy()
+        for stage in (1, 2, 3):
+            c1, c2, c3 = RK_C[stage - 1]
+            o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=c1, RK1=c2, dt=dt*c3)
+            f["Conserved"] = np.ascontiguousarray((c1*f["Conserved_old"] + c2*f["Conserved"]) + (c3*f["Conserved_t"])*dt)
+            o.update_primitive_from_conserved(f)
+            o.update_properties_from_primitive(f)
+        s.TimeStep(fl, scheme, dt, diffusion=True, chemistry=chem, vorticityScale=1.0)
+        got = fl.download(names)
+        for k in names:
+            e = rel_err(got[k], f[k])
+            assert e <= TOL_CHEM, (step, k, e)
+    # the step moved the state (the comparison is not between two copies of the initial condition)
+    assert rel_err(f["Conserved"], f["Conserved_old"]) > 1e-4
