@@ -347,6 +347,29 @@ def run_gpu(args, rank, world, local_rank):
                    "includes": "H2D Conserved+T (z-slab pipeline), UpdatePrimitiveFromConserved, UpdatePropertiesFromPrimitive, sensors, UpdateDerivatives, D2H Conserved_t+T"}
         except Exception as ex:   # report, never silently drop
             e2e = {"value": None, "unit": "cell-updates/s", "error": repr(ex)[:200]}
+    # ---- whole RK3 time step (sensors + 3 x (UpdateDerivatives, UpdateVars + primitive/property recovery)) ----
+    # extra information beside the headline metric; run last because it advances the state
+    tstep = None
+    if rank == 0 and world == 1:
+        try:
+            dts = 1e-7
+            solver.TimeStep(fl, scheme, dts, diffusion, chemistry, 1.0, tile=tile, bounds=bounds)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(3):
+                solver.TimeStep(fl, scheme, dts, diffusion, chemistry, 1.0, tile=tile, bounds=bounds)
+            b.record(); torch.cuda.synchronize()
+            tms = a.elapsed_time(b) / 3
+            a.record()
+            for st in (1, 2, 3):
+                solver.UpdateVarsAndRecover(fl, st, dts, False, tile=tile)
+            b.record(); torch.cuda.synchronize()
+            tstep = {"ms_per_time_step": tms, "cell_time_steps_per_s": cells_rank / (tms * 1e-3),
+                     "rk_stage_ms": a.elapsed_time(b) / 3, "finite": bool(torch.isfinite(fl.t["Conserved"]).all().item()),
+                     "includes": "UpdateShockSensors, InitializeTemporaries, 3 x (htr_rhs, htr_rk_stage)"}
+        except Exception as ex:
+            tstep = {"error": repr(ex)[:200]}
     if rank != 0:
         return
 
@@ -396,7 +419,7 @@ def run_gpu(args, rank, world, local_rank):
                        "smooth_fraction": smooth, "l2": "inputs larger than L2 (no flush needed)" if n >= 128 else "inputs may fit L2",
                        "halo": "none (periodic wrap by index)" if world == 1 else "3 ghost planes, NCCL send/recv per step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-            "roofline": roof, "cpu_baseline": cpu, "build": solver.L.htr_build_info().decode()}
+            "roofline": roof, "cpu_baseline": cpu, "time_step": tstep, "build": solver.L.htr_build_info().decode()}
     emit(json.dumps(line))
 
 

@@ -394,9 +394,16 @@ __device__ __forceinline__ void storeProperties(const htr_fluid &f, const Pt &p,
    double Yi[nSpec], Di[nSpec];
    const double MixW = mix::GetMolarWeightFromXi(Xi);
    *at<double>(f.rho, p) = mix::GetRho(P, T, MixW);
+#if HTR_MULTICOMP && !defined(HTR_EXACT_POW)
+   double mu, lam;
+   mix::GetTransport(mu, lam, Di, P, T, MixW, Xi);
+   *at<double>(f.mu, p) = mu;
+   *at<double>(f.lam, p) = lam;
+#else
    *at<double>(f.mu, p) = mix::GetViscosity(T, Xi);
    *at<double>(f.lam, p) = mix::GetHeatConductivity(T, Xi);
    mix::GetDiffusivity(Di, P, T, MixW, Xi);
+#endif
    mix::GetMassFractions(Yi, MixW, Xi);
    const double gamma = mix::GetGamma(T, MixW, Yi);
    *at<double>(f.SoS, p) = mix::GetSpeedOfSound(T, gamma, MixW);
@@ -740,7 +747,11 @@ int htr_set_mixture(const void *mix, size_t bytes) {
             tr.sigmaij[i][j] = 0.5*(a.diff.sigma + b.diff.sigma)*pow(xi, -1./6);
             tr.kboEpsij[i][j] = sqrt(a.diff.kbOveps*b.diff.kbOveps)/(xi*xi);
             tr.invWij[i][j] = (a.W + b.W)/(a.W*b.W);
+            tr.is8[i][j] = 1.0/tr.s8[i][j];
+            tr.cdif[i][j] = 16*PI*tr.sigmaij[i][j]*tr.sigmaij[i][j]/(3*sqrt(2*PI*tr.kb3*Na*tr.invWij[i][j]));
          }
+         tr.cmu[i] = 5*sqrt(PI*a.W/Na*kb)/(16*PI*tr.sigma2[i]);
+         tr.zf[i] = a.diff.Z298*tr.fz298[i];
       }
       if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_tr, &tr, sizeof(tr));
    }

@@ -28,6 +28,11 @@ struct TransDerived {
    double kboEpsij[HTR_NSPEC][HTR_NSPEC];
    double invWij[HTR_NSPEC][HTR_NSPEC];
    double pi15, kb3;                         // pow(PI, 1.5), pow(kb, 3)
+   // production build only (GetTransport): the temperature-independent factors of the kinetic-theory formulas
+   double cmu[HTR_NSPEC];                    // mu_i = cmu_i sqrt(T)/Omega_mu(T*_i)
+   double is8[HTR_NSPEC][HTR_NSPEC];         // 1/s8
+   double cdif[HTR_NSPEC][HTR_NSPEC];        // 1/D_ij = cdif_ij P Omega_D(T*_ij)/T^1.5, i > j
+   double zf[HTR_NSPEC];                     // Z298 * fz298
 };
 __constant__ TransDerived c_tr;
 #endif
@@ -318,6 +323,94 @@ HTR_DEV void GetDiffusivity(double *Di, double Pn, double Tn, double MixW, const
       Di[i] = num/(MixW*Di[i])*c_mix.iDiRef;
    }
 }
+#ifndef HTR_EXACT_POW
+// mu, lam and Di of one state in one pass (production build).  Same kinetic-theory formulas as GetViscosity /
+// GetHeatConductivity / GetDiffusivity above, regrouped so that every cell evaluates one sqrt(T), one division per
+// collision integral and reciprocal square roots instead of quotient-then-root chains:
+//    mu_i  = cmu_i sqrt(T)/Omega_mu_i                         D_kk/mu_k = 1.2 Omega_mu_k/Omega_D_k
+//    sqrt(mu_i/mu_j) = sqrt(mu_i) rsqrt(mu_j)                 1/D_ij = cdif_ij P Omega_D_ij/T^1.5
+// The regrouping changes rounding only (a few ulp per property; parity tests hold it to 1e-10 against the reference).
+HTR_DEV void GetTransport(double &muOut, double &lamOut, double *Di, double Pn, double Tn, double MixW, const double *Xi) {
+   const double T = Tn*c_mix.TRef;
+   const double P = Pn*c_mix.PRef;
+   const double sqrtT = sqrt(T);
+   const double Tinv = 1.0/T;
+   double muk[nSpec], a = 0.0, b = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      const SpeciesData &s = c_mix.species[i];
+      const double Ts = T*s.diff.kbOveps;
+      const double nm = 3.3530622607 + Ts*(2.53272006 + Ts*(2.9024238575 + Ts*0.11186138893));
+      const double dm = 0.8662326188 + Ts*(1.3913958626 + Ts*(3.158490576 + Ts*(0.18973411754 + Ts*0.00018682962894)));
+      double lami;
+      if (s.diff.Geom == 0) {
+         muk[i] = c_tr.cmu[i]*sqrtT*dm/nm;
+         lami = 15.0/4*muk[i]*c_der[i].rOvW;
+      } else {
+         const double nd = 6.8728271691 + Ts*(9.4122316321 + Ts*(7.7442359037 + Ts*0.23424661229));
+         const double dd = 1.45337701568 + Ts*(5.2269794238 + Ts*(9.7108519575 + Ts*(0.46539437353 + Ts*0.00041908394781)));
+         const double inv = 1.0/(nm*dm*nd);                    // one division for both quotients
+         muk[i] = c_tr.cmu[i]*sqrtT*(dm*dm*nd*inv);
+         const double fV = 1.2*(nm*nm*dd*inv);
+         const bool lin = (s.diff.Geom == 1);
+         const double CvROvR = lin ? 1.0 : 1.5;
+         const double CvT = 1.5*RGAS;
+         const double CvR = CvROvR*RGAS;
+         const double CvV = spec::GetCp(s, c_der[i], T, Tinv)*s.W - (lin ? 3.5 : 4.0)*RGAS;
+         const double rs = rsqrt(Ts), tmp = rs*rs;
+         const double F = 1 + 0.5*c_tr.pi15*rs + (2 + 0.25*PI*PI)*tmp + c_tr.pi15*tmp*rs;
+         const double A = 2.5 - fV;
+         const double c = 2/PI*(5./3*CvROvR + fV);
+         const double iB = F/(c_tr.zf[i] + c*F);              // 1/(Zrot + c), Zrot = zf/F
+         const double fT = 2.5*(1. - 2*CvR*A*iB/(PI*CvT));
+         const double fR = fV*(1. + 2*A*iB/PI);
+         lami = muk[i]*(fT*CvT + fR*CvR + fV*CvV)/s.W;
+      }
+      a += Xi[i]*lami;
+      b += Xi[i]/lami;
+   }
+   lamOut = 0.5*(a + 1.0/b)*c_mix.ilamRef;
+   double sm[nSpec], ism[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) { ism[i] = rsqrt(muk[i]); sm[i] = muk[i]*ism[i]; }
+   double mu = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      double den = 0.0;
+      HTR_UNROLL
+      for (int j = 0; j < nSpec; j++) {
+         const double Phi = 1 + sm[i]*ism[j]*c_tr.w25[i][j];
+         den += Xi[j]*(Phi*Phi*c_tr.is8[i][j]);
+      }
+      mu += Xi[i]*muk[i]/den;
+   }
+   muOut = mu*c_mix.imuRef;
+   const double pt = P*Tinv/sqrtT;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) Di[i] = 0.0;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      HTR_UNROLL
+      for (int j = 0; j < i; j++) {
+         const double Ts = T*c_tr.kboEpsij[i][j];
+         const double nd = 6.8728271691 + Ts*(9.4122316321 + Ts*(7.7442359037 + Ts*0.23424661229));
+         const double dd = 1.45337701568 + Ts*(5.2269794238 + Ts*(9.7108519575 + Ts*(0.46539437353 + Ts*0.00041908394781)));
+         const double invDij = c_tr.cdif[i][j]*pt*nd/dd;
+         Di[i] += Xi[j]*invDij;
+         Di[j] += Xi[i]*invDij;
+      }
+   }
+   const double iW = c_mix.iDiRef/MixW;
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) {
+      double num = 0.0;
+      HTR_UNROLL
+      for (int j = 0; j < nSpec; j++)
+         if (j != i) num += Xi[j]*c_mix.species[j].W;
+      Di[i] = num*iW/Di[i];
+   }
+}
+#endif
 HTR_DEV double Getdpde(double rho, double gamma) { return rho*(gamma - 1); }
 HTR_DEV void Getdpdrhoi(double *dpdrhoi, double gamma, double Tn, const double *Yi) {
    const double T = Tn*c_mix.TRef;
