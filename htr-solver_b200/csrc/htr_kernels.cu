@@ -436,6 +436,32 @@ __global__ void __launch_bounds__(128) rk_initialize_time_derivatives_kernel(con
    }
 }
 
+// The same three operations when the nEq doubles of consecutive x cells are contiguous (stride[0] == 8*nEq, every
+// layout the library allocates): a row of the tile is a flat array of nx*nEq doubles and one thread moves one double,
+// so every warp access is a full 256-byte line instead of 32 spans 72 bytes apart.
+// OP 0: Conserved_old = Conserved   1: Conserved_t = 0   2: Conserved_t = -Conserved_t_old   3: UpdateVars(stage)
+template<int OP>
+__global__ void __launch_bounds__(256) rk_rows_kernel(const htr_fluid f, const htr_rect tile, const int stage, const double dt) {
+   const int64_t e = (int64_t)blockIdx.x*256 + threadIdx.x;
+   if (e >= (tile.hi[0] - tile.lo[0] + 1)*(int64_t)nEq) return;
+   Pt p; p.x = tile.lo[0]; p.y = tile.lo[1] + blockIdx.y; p.z = tile.lo[2] + blockIdx.z;
+   if (OP == 0) at<double>(f.Conserved_old, p)[e] = at<const double>(f.Conserved, p)[e];
+   if (OP == 1) at<double>(f.Conserved_t, p)[e] = 0.0;
+   if (OP == 2) at<double>(f.Conserved_t, p)[e] = -at<const double>(f.Conserved_t_old, p)[e];
+   if (OP == 3) {
+      const double c1 = c_rk[stage][0], c2 = c_rk[stage][1], c3 = c_rk[stage][2];
+      double *C = at<double>(f.Conserved, p) + e;
+      *C = (c1*at<const double>(f.Conserved_old, p)[e] + c2*(*C)) + (c3*at<const double>(f.Conserved_t, p)[e])*dt;
+   }
+}
+static bool rowsContiguous(std::initializer_list<const htr_acc*> fields, const htr_rect &t) {
+   for (const htr_acc *a : fields) if (a->stride[0] != 8*nEq) return false;
+   return (t.hi[1] - t.lo[1]) < 65535 && (t.hi[2] - t.lo[2]) < 65535;
+}
+static dim3 rowsGrid(const htr_rect &t) {
+   return dim3((unsigned)(((t.hi[0] - t.lo[0] + 1)*(int64_t)nEq + 255)/256), (unsigned)(t.hi[1] - t.lo[1] + 1), (unsigned)(t.hi[2] - t.lo[2] + 1));
+}
+
 // UpdateVars(STAGE); with RECOVER also UpdatePrimitiveFromConserved and UpdatePropertiesFromPrimitive of the
 // same cell from the registers (the three tasks the reference launches back to back after every stage,
 // src/prometeo.rg:1427, :452, :470).  The operation order of each task is kept, so the fused pass writes the
@@ -467,7 +493,86 @@ __global__ void __launch_bounds__(128) rk_update_vars_kernel(const htr_fluid f, 
    }
 }
 
-__global__ void __launch_bounds__(128) properties_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
+// The fused stage with 128 consecutive x cells per block and every multi-component field moved as flat row spans
+// through shared memory (coalesced 8-byte accesses; the per-cell view in shared memory has an odd stride in doubles,
+// hence no bank conflicts).  Needs x-contiguous cells in all AoS fields (rkStageRowsOK); same arithmetic and bits
+// as rk_update_vars_kernel<true>.
+#ifndef HTR_RKS_MINB
+#define HTR_RKS_MINB 6
+#endif
+constexpr int RKS_NT = 128;
+constexpr int RKS_POOL = RKS_NT*((3*nEq > nEq + 3*nSpec + 3) ? 3*nEq : nEq + 3*nSpec + 3);
+__global__ void __launch_bounds__(RKS_NT, HTR_RKS_MINB) rk_stage_rows_kernel(const htr_fluid f, const htr_rect tile, const int stage, const double dt) {
+   __shared__ double pool[RKS_POOL];
+   const int tid = threadIdx.x;
+   const int x0 = blockIdx.x*RKS_NT;
+   const int nx = (int)(tile.hi[0] - tile.lo[0] + 1);
+   const int nc = min(RKS_NT, nx - x0);                      // cells of this block
+   Pt p0; p0.x = tile.lo[0] + x0; p0.y = tile.lo[1] + blockIdx.y; p0.z = tile.lo[2] + blockIdx.z;
+   {
+      const double *gCo = at<const double>(f.Conserved_old, p0), *gC = at<const double>(f.Conserved, p0), *gCt = at<const double>(f.Conserved_t, p0);
+      for (int e = tid; e < nc*nEq; e += RKS_NT) {
+         pool[e] = gCo[e]; pool[RKS_NT*nEq + e] = gC[e]; pool[2*RKS_NT*nEq + e] = gCt[e];
+      }
+   }
+   __syncthreads();
+   const bool valid = tid < nc;
+   Pt p = p0; p.x += tid;
+   const double c1 = c_rk[stage][0], c2 = c_rk[stage][1], c3 = c_rk[stage][2];
+   double U[nEq], Xi[nSpec], u[3], Yi[nSpec], Di[nSpec];
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++)
+      U[i] = (c1*pool[tid*nEq + i] + c2*pool[RKS_NT*nEq + tid*nEq + i]) + (c3*pool[2*RKS_NT*nEq + tid*nEq + i])*dt;
+   __syncthreads();
+   if (valid) {
+      double rho, MixW, P;
+      double T = *at<double>(f.temperature, p);
+      primitivesFromConserved(U, rho, Yi, MixW, u, T, P);
+      mix::GetMolarFractions(Xi, MixW, Yi);
+      *at<double>(f.temperature, p) = T;
+      *at<double>(f.pressure, p) = P;
+      // storeProperties, with the vector outputs kept in registers
+      const double MixW2 = mix::GetMolarWeightFromXi(Xi);
+      *at<double>(f.rho, p) = mix::GetRho(P, T, MixW2);
+#if HTR_MULTICOMP && !defined(HTR_EXACT_POW)
+      double mu, lam;
+      mix::GetTransport(mu, lam, Di, P, T, MixW2, Xi);
+      *at<double>(f.mu, p) = mu;
+      *at<double>(f.lam, p) = lam;
+#else
+      *at<double>(f.mu, p) = mix::GetViscosity(T, Xi);
+      *at<double>(f.lam, p) = mix::GetHeatConductivity(T, Xi);
+      mix::GetDiffusivity(Di, P, T, MixW2, Xi);
+#endif
+      mix::GetMassFractions(Yi, MixW2, Xi);
+      const double gamma = mix::GetGamma(T, MixW2, Yi);
+      *at<double>(f.SoS, p) = mix::GetSpeedOfSound(T, gamma, MixW2);
+   }
+   double *sC = pool, *sX = sC + RKS_NT*nEq, *sY = sX + RKS_NT*nSpec, *sD = sY + RKS_NT*nSpec, *sV = sD + RKS_NT*nSpec;
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) sC[tid*nEq + i] = U[i];
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) { sX[tid*nSpec + i] = Xi[i]; sY[tid*nSpec + i] = Yi[i]; sD[tid*nSpec + i] = Di[i]; }
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) sV[tid*3 + i] = u[i];
+   __syncthreads();
+   {
+      double *gC = at<double>(f.Conserved, p0), *gX = at<double>(f.MolarFracs, p0), *gY = at<double>(f.MassFracs, p0);
+      double *gD = at<double>(f.Di, p0), *gV = at<double>(f.velocity, p0);
+      for (int e = tid; e < nc*nEq; e += RKS_NT) gC[e] = sC[e];
+      for (int e = tid; e < nc*nSpec; e += RKS_NT) { gX[e] = sX[e]; gY[e] = sY[e]; gD[e] = sD[e]; }
+      for (int e = tid; e < nc*3; e += RKS_NT) gV[e] = sV[e];
+   }
+}
+static bool rkStageRowsOK(const htr_fluid &f, const htr_rect &t) {
+   return rowsContiguous({&f.Conserved, &f.Conserved_old, &f.Conserved_t}, t) && f.MolarFracs.stride[0] == 8*nSpec &&
+          f.MassFracs.stride[0] == 8*nSpec && f.Di.stride[0] == 8*nSpec && f.velocity.stride[0] == 24;
+}
+
+#ifndef HTR_PROP_MINB
+#define HTR_PROP_MINB 6
+#endif
+__global__ void __launch_bounds__(128, HTR_PROP_MINB) properties_from_primitive_kernel(const htr_fluid f, const htr_rect tile) {
    Pt p; if (!cellOf(p, tile)) return;
    double Xi[nSpec];
    HTR_UNROLL
@@ -840,19 +945,31 @@ int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *til
 }
 int htr_rk_initialize_temporaries(const htr_fluid *f, const htr_rect *tile, void *stream) {
    HTR_CHECK_COMMON(f, tile)
-   rk_initialize_temporaries_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   if (rowsContiguous({&f->Conserved, &f->Conserved_old}, *tile))
+      rk_rows_kernel<0><<<rowsGrid(*tile), 256, 0, (cudaStream_t)stream>>>(*f, *tile, 0, 0.0);
+   else
+      rk_initialize_temporaries_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
    return cuerr(cudaGetLastError());
 }
 int htr_rk_initialize_time_derivatives(const htr_fluid *f, const htr_rect *tile, int implicitChemistry, void *stream) {
    HTR_CHECK_COMMON(f, tile)
-   rk_initialize_time_derivatives_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, implicitChemistry);
+   if (rowsContiguous({&f->Conserved_t, implicitChemistry ? &f->Conserved_t_old : &f->Conserved_t}, *tile)) {
+      if (implicitChemistry) rk_rows_kernel<2><<<rowsGrid(*tile), 256, 0, (cudaStream_t)stream>>>(*f, *tile, 0, 0.0);
+      else rk_rows_kernel<1><<<rowsGrid(*tile), 256, 0, (cudaStream_t)stream>>>(*f, *tile, 0, 0.0);
+   } else
+      rk_initialize_time_derivatives_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, implicitChemistry);
    return cuerr(cudaGetLastError());
 }
 static int rkUpdate(bool recover, int stage, double dt, int implicitChemistry, const htr_fluid *f, const htr_rect *tile, void *stream) {
    HTR_CHECK_COMMON(f, tile)
    if (stage < 1 || stage > 3) return HTR_EINVAL;
    if (implicitChemistry) dt *= 0.5;
-   if (recover) rk_update_vars_kernel<true><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
+   if (recover && rkStageRowsOK(*f, *tile) && !g_no_fast)
+      rk_stage_rows_kernel<<<dim3((unsigned)((tile->hi[0] - tile->lo[0] + RKS_NT)/RKS_NT), (unsigned)(tile->hi[1] - tile->lo[1] + 1),
+                                  (unsigned)(tile->hi[2] - tile->lo[2] + 1)), RKS_NT, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
+   else if (recover) rk_update_vars_kernel<true><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
+   else if (rowsContiguous({&f->Conserved, &f->Conserved_old, &f->Conserved_t}, *tile))
+      rk_rows_kernel<3><<<rowsGrid(*tile), 256, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
    else rk_update_vars_kernel<false><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, stage - 1, dt);
    return cuerr(cudaGetLastError());
 }
