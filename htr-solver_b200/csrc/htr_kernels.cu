@@ -465,7 +465,7 @@ static dim3 rowsGrid(const htr_rect &t) {
 // UpdateVars(STAGE); with RECOVER also UpdatePrimitiveFromConserved and UpdatePropertiesFromPrimitive of the
 // same cell from the registers (the three tasks the reference launches back to back after every stage,
 // src/prometeo.rg:1427, :452, :470).  The operation order of each task is kept, so the fused pass writes the
-// same bits as the three kernels in sequence.
+// same bits as the three kernels in sequence (strict build; FMA contraction may differ by an ulp otherwise).
 template<bool RECOVER>
 __global__ void __launch_bounds__(128) rk_update_vars_kernel(const htr_fluid f, const htr_rect tile, const int stage, const double dt) {
    Pt p; if (!cellOf(p, tile)) return;

@@ -116,7 +116,9 @@ int htr_update_conserved_from_primitive(const htr_fluid *f, const htr_rect *tile
  *   htr_rk_stage                        UpdateVars(STAGE) + UpdatePrimitiveFromConserved +
  *                                       UpdatePropertiesFromPrimitive in one pass over the tile (the three
  *                                       launches of src/prometeo.rg:1427, :452, :470 when the tile has no
- *                                       boundary nodes); same bits as the three calls in sequence */
+ *                                       boundary nodes); same operations in the same order as the three calls in sequence
+ *                                       (bit-identical in the strict build; FMA contraction may differ by an ulp
+ *                                       in the production build) */
 int htr_rk_initialize_temporaries(const htr_fluid *f, const htr_rect *tile, void *stream);
 int htr_rk_initialize_time_derivatives(const htr_fluid *f, const htr_rect *tile, int implicitChemistry, void *stream);
 int htr_rk_update_vars(int stage, double Integrator_deltaTime, int implicitChemistry, const htr_fluid *f,

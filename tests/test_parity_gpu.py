@@ -415,8 +415,15 @@ def test_rk_glue(cfg, kw, implicit):
                 fl.t[k].copy_(v)
             s.UpdateVarsAndRecover(fl, stage, dt, implicit)
             fused = fl.download(names)
+            def same(a, b, k):
+                # without FMA contraction the fused pass repeats the three tasks bit for bit; with it the compiler
+                # contracts the joined expression trees differently (an ulp here and there)
+                if variant == "strict":
+                    assert np.array_equal(a[k], b[k]), (variant, stage, k)
+                else:
+                    assert rel_err(a[k], b[k]) <= 1e-14, (variant, stage, k, rel_err(a[k], b[k]))
             for k in names:
-                assert np.array_equal(fused[k], seq[k]), (variant, stage, k)
+                same(fused, seq, k)
             # the per-cell form of the fused kernel (layouts whose rows are not contiguous fall back to it)
             for k, v in before.items():
                 fl.t[k].copy_(v)
@@ -425,7 +432,7 @@ def test_rk_glue(cfg, kw, implicit):
             s.set_option("fast", 1)
             percell = fl.download(names)
             for k in names:
-                assert np.array_equal(percell[k], seq[k]), (variant, stage, k)
+                same(percell, seq, k)
             # against the reference tasks on the numpy update
             o.update_primitive_from_conserved(h)
             o.update_properties_from_primitive(h)
