@@ -1076,19 +1076,26 @@ static void *cellPtr(const htr_acc &a, const htr_rect &t) {
 }
 
 // z-slab pipeline of htr_host_rhs: uploads (copy stream), device work (caller's stream) and downloads (second copy
-// stream) of different slabs overlap.  Stage dependencies across slabs (stencil reach 3 planes < slab thickness):
-//   P(k) primitives+properties  <- upload k           D(k) Ducros       <- P(k-1..k+1)
-//   S(k) shock sensors          <- D(k-1..k+1)        R(k) htr_rhs      <- S(k-1..k+1), P(k-1..k+1)
-// Slab neighbours are taken modulo the slab count (periodic boxes wrap; for bounded boxes this only delays work).
-struct HostPipe { cudaStream_t up, down; cudaEvent_t evUp[16], evR[16], evStart, evDone; bool ok; };
+// stream) of different slabs overlap.  The stages of a slab are skewed in z by the reach of their stencils, so every
+// stage only needs planes whose previous stage has already been issued on the same stream:
+//   P  primitives+properties of the uploaded planes [z0, z1]
+//   D  Ducros sensor of        [z0 - 2, z1 - 2]      (velocity gradients: 1 plane, 2 on one-sided nodes)
+//   S  shock sensors of        [z0 - 5, z1 - 5]      (6-point stencil: 3 planes of Conserved and Ducros)
+//   R  htr_rhs + download of   [z0 - 8, z1 - 8]      (3 planes of state, properties and sensors)
+// The first planes of each stage (whose stencils reach back across the periodic wrap to planes that are uploaded last)
+// and the last ones are done after the last upload: 2 x 8 planes.  A download therefore trails its upload by one slab
+// and 8 planes, and the call takes about max(H2D, D2H) of the whole state plus that lag.
+constexpr int PIPE_MAXSLABS = 64;
+struct HostPipe { cudaStream_t up, down; cudaEvent_t evUp[PIPE_MAXSLABS], evR[PIPE_MAXSLABS + 2], evStart, evDone; bool ok; };
 static HostPipe g_pipe = {};
 static bool pipeInit() {
    if (g_pipe.ok) return true;
    if (cudaStreamCreateWithFlags(&g_pipe.up, cudaStreamNonBlocking) != cudaSuccess) return false;
    if (cudaStreamCreateWithFlags(&g_pipe.down, cudaStreamNonBlocking) != cudaSuccess) return false;
-   for (int i = 0; i < 16; i++)
-      if (cudaEventCreateWithFlags(&g_pipe.evUp[i], cudaEventDisableTiming) != cudaSuccess ||
-          cudaEventCreateWithFlags(&g_pipe.evR[i], cudaEventDisableTiming) != cudaSuccess) return false;
+   for (int i = 0; i < PIPE_MAXSLABS; i++)
+      if (cudaEventCreateWithFlags(&g_pipe.evUp[i], cudaEventDisableTiming) != cudaSuccess) return false;
+   for (int i = 0; i < PIPE_MAXSLABS + 2; i++)
+      if (cudaEventCreateWithFlags(&g_pipe.evR[i], cudaEventDisableTiming) != cudaSuccess) return false;
    if (cudaEventCreateWithFlags(&g_pipe.evStart, cudaEventDisableTiming) != cudaSuccess) return false;
    if (cudaEventCreateWithFlags(&g_pipe.evDone, cudaEventDisableTiming) != cudaSuccess) return false;
    g_pipe.ok = true;
@@ -1107,84 +1114,98 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
    const int64_t nx = tile->hi[0] - tile->lo[0] + 1, ny = tile->hi[1] - tile->lo[1] + 1, nz = tile->hi[2] - tile->lo[2] + 1;
    const bool needOld = (nSpec > 1 && scheme != HTR_SCHEME_SKEWSYMMETRIC);
    const bool sensors = update_sensors && scheme == HTR_SCHEME_HYBRID;
-   const int ns = (nz >= 128 && !g_no_pipe && pipeInit()) ? 16 : 1;
+   // slab thickness: a multiple of the 15 planes one CTA of the Euler-z kernel updates
+   int64_t T = (nz >= 400) ? 30 : 15;
+   while ((nz + T - 1)/T > PIPE_MAXSLABS) T += 15;
+   const bool pipelined = nz >= 60 && !g_no_pipe && pipeInit();
+   const int ns = pipelined ? (int)((nz + T - 1)/T) : 1;
    cudaError_t e;
    int rc;
-   auto slab = [&](int k) {           // z range of slab k (modulo ns)
-      k = ((k % ns) + ns) % ns;
-      htr_rect r = *tile;
-      r.lo[2] = tile->lo[2] + nz*k/ns;
-      r.hi[2] = tile->lo[2] + nz*(k + 1)/ns - 1;
-      return r;
-   };
-   auto upload = [&](int k, cudaStream_t s) -> cudaError_t {
-      const htr_rect r = slab(k);
-      const size_t off = (size_t)(r.lo[2] - tile->lo[2])*nx*ny, cells = (size_t)(r.hi[2] - r.lo[2] + 1)*nx*ny;
+   // all ranges below are planes relative to the tile, inclusive; empty ranges are skipped
+   auto box = [&](int64_t zlo, int64_t zhi) { htr_rect r = *tile; r.lo[2] = tile->lo[2] + zlo; r.hi[2] = tile->lo[2] + zhi; return r; };
+   auto upload = [&](int64_t zlo, int64_t zhi, cudaStream_t s) -> cudaError_t {
+      if (zlo > zhi) return cudaSuccess;
+      const htr_rect r = box(zlo, zhi);
+      const size_t off = (size_t)zlo*nx*ny, cells = (size_t)(zhi - zlo + 1)*nx*ny;
       cudaError_t q;
       if ((q = cudaMemcpyAsync(cellPtr(f->Conserved, r), h_Conserved + off*nEq, cells*8*nEq, cudaMemcpyHostToDevice, s)) != cudaSuccess) return q;
       if (needOld && h_Conserved_old &&
           (q = cudaMemcpyAsync(cellPtr(f->Conserved_old, r), h_Conserved_old + off*nEq, cells*8*nEq, cudaMemcpyHostToDevice, s)) != cudaSuccess) return q;
       return cudaMemcpyAsync(cellPtr(f->temperature, r), h_temperature + off, cells*8, cudaMemcpyHostToDevice, s);
    };
-   auto download = [&](int k, cudaStream_t s) -> cudaError_t {
-      const htr_rect r = slab(k);
-      const size_t off = (size_t)(r.lo[2] - tile->lo[2])*nx*ny, cells = (size_t)(r.hi[2] - r.lo[2] + 1)*nx*ny;
+   auto download = [&](int64_t zlo, int64_t zhi, cudaStream_t s) -> cudaError_t {
+      const htr_rect r = box(zlo, zhi);
+      const size_t off = (size_t)zlo*nx*ny, cells = (size_t)(zhi - zlo + 1)*nx*ny;
       cudaError_t q;
       if ((q = cudaMemcpyAsync(h_Conserved_t + off*nEq, cellPtr(f->Conserved_t, r), cells*8*nEq, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return q;
       return cudaMemcpyAsync(h_temperature + off, cellPtr(f->temperature, r), cells*8, cudaMemcpyDeviceToHost, s);
    };
-   auto P = [&](int k) -> int {
-      const htr_rect r = slab(k);
+   auto P = [&](int64_t zlo, int64_t zhi) -> int {
+      if (zlo > zhi) return HTR_OK;
+      const htr_rect r = box(zlo, zhi);
       int q;
       if ((q = htr_update_primitive_from_conserved(f, &r, stream)) != HTR_OK) return q;
       if ((q = htr_update_properties_from_primitive(f, &r, stream)) != HTR_OK) return q;
       if (needOld && !h_Conserved_old) {       // no separate old state: device copy instead of a second upload
-         const size_t cells = (size_t)(r.hi[2] - r.lo[2] + 1)*nx*ny;
+         const size_t cells = (size_t)(zhi - zlo + 1)*nx*ny;
          if (cudaMemcpyAsync(cellPtr(f->Conserved_old, r), cellPtr(f->Conserved, r), cells*8*nEq, cudaMemcpyDeviceToDevice, st) != cudaSuccess) return 1000;
       }
       return HTR_OK;
    };
-   auto D = [&](int k) -> int { const htr_rect r = slab(k); return sensors ? htr_ducros_sensor(f, &r, bounds, vorticityScale, stream) : HTR_OK; };
-   auto S = [&](int k) -> int {
-      if (!sensors) return HTR_OK;
-      const htr_rect r = slab(k);
+   auto D = [&](int64_t zlo, int64_t zhi) -> int {
+      if (!sensors || zlo > zhi) return HTR_OK;
+      const htr_rect r = box(zlo, zhi);
+      return htr_ducros_sensor(f, &r, bounds, vorticityScale, stream);
+   };
+   auto S = [&](int64_t zlo, int64_t zhi) -> int {
+      if (!sensors || zlo > zhi) return HTR_OK;
+      const htr_rect r = box(zlo, zhi);
       for (int d = 0; d < 3; d++) { const int q = htr_shock_sensor(d, f, &r, bounds, stream); if (q != HTR_OK) return q; }
       return HTR_OK;
    };
-   auto R = [&](int k) -> int { const htr_rect r = slab(k); return htr_rhs(scheme, diffusion, chemistry, f, &r, bounds, RK0, RK1, deltaTime, stream); };
+   auto R = [&](int64_t zlo, int64_t zhi) -> int {
+      const htr_rect r = box(zlo, zhi);
+      return htr_rhs(scheme, diffusion, chemistry, f, &r, bounds, RK0, RK1, deltaTime, stream);
+   };
 
    if (ns == 1) {
-      if ((e = upload(0, st)) != cudaSuccess) return cuerr(e);
-      if ((rc = P(0)) != HTR_OK || (rc = D(0)) != HTR_OK || (rc = S(0)) != HTR_OK || (rc = R(0)) != HTR_OK) return rc;
-      return cuerr(download(0, st));
+      if ((e = upload(0, nz - 1, st)) != cudaSuccess) return cuerr(e);
+      if ((rc = P(0, nz - 1)) != HTR_OK || (rc = D(0, nz - 1)) != HTR_OK || (rc = S(0, nz - 1)) != HTR_OK || (rc = R(0, nz - 1)) != HTR_OK) return rc;
+      return cuerr(download(0, nz - 1, st));
    }
    // the copy streams start after whatever the caller queued before this call
    if ((e = cudaEventRecord(g_pipe.evStart, st)) != cudaSuccess) return cuerr(e);
    cudaStreamWaitEvent(g_pipe.up, g_pipe.evStart, 0);
    cudaStreamWaitEvent(g_pipe.down, g_pipe.evStart, 0);
    for (int k = 0; k < ns; k++) {
-      if ((e = upload(k, g_pipe.up)) != cudaSuccess) return cuerr(e);
+      const int64_t z0 = k*T, z1 = (z0 + T < nz ? z0 + T : nz) - 1;
+      if ((e = upload(z0, z1, g_pipe.up)) != cudaSuccess) return cuerr(e);
       cudaEventRecord(g_pipe.evUp[k], g_pipe.up);
    }
-   auto finish = [&](int k) -> int {          // R(k) then its download
-      int q = R(k);
+   int nfin = 0;
+   auto finish = [&](int64_t zlo, int64_t zhi) -> int {          // R then its download
+      if (zlo > zhi) return HTR_OK;
+      int q = R(zlo, zhi);
       if (q != HTR_OK) return q;
-      cudaEventRecord(g_pipe.evR[k], st);
-      cudaStreamWaitEvent(g_pipe.down, g_pipe.evR[k], 0);
-      return cuerr(download(k, g_pipe.down));
+      cudaEventRecord(g_pipe.evR[nfin], st);
+      cudaStreamWaitEvent(g_pipe.down, g_pipe.evR[nfin], 0);
+      nfin++;
+      return cuerr(download(zlo, zhi, g_pipe.down));
    };
-   // stage s of slab j may run once stage s-1 of j-1, j, j+1 has been issued (same stream: issue order = execution order)
+   const int64_t dD = sensors ? 2 : 0, dS = sensors ? dD + 3 : 0, dR = dS + 3;
+   auto lo = [](int64_t z, int64_t d) { return z - d > d ? z - d : d; };
    for (int k = 0; k < ns; k++) {
+      const int64_t z0 = k*T, z1 = (z0 + T < nz ? z0 + T : nz) - 1;
       cudaStreamWaitEvent(st, g_pipe.evUp[k], 0);
-      if ((rc = P(k)) != HTR_OK) return rc;
-      if (k >= 2 && (rc = D(k - 1)) != HTR_OK) return rc;              // D(1 .. ns-2)
-      if (k >= 4 && (rc = S(k - 2)) != HTR_OK) return rc;              // S(2 .. ns-3)
-      if (k >= 6 && (rc = finish(k - 3)) != HTR_OK) return rc;         // R(3 .. ns-4)
+      if ((rc = P(z0, z1)) != HTR_OK) return rc;
+      if ((rc = D(lo(z0, dD), z1 - dD)) != HTR_OK) return rc;
+      if ((rc = S(lo(z0, dS), z1 - dS)) != HTR_OK) return rc;
+      if ((rc = finish(lo(z0, dR), z1 - dR)) != HTR_OK) return rc;
    }
-   if ((rc = D(ns - 1)) != HTR_OK || (rc = D(0)) != HTR_OK) return rc;
-   if ((rc = S(ns - 2)) != HTR_OK || (rc = S(ns - 1)) != HTR_OK || (rc = S(0)) != HTR_OK || (rc = S(1)) != HTR_OK) return rc;
-   for (int k : {ns - 3, ns - 2, ns - 1, 0, 1, 2})
-      if ((rc = finish(k)) != HTR_OK) return rc;
+   // the planes next to the wrap (all uploads are in)
+   if ((rc = D(nz - dD, nz - 1)) != HTR_OK || (rc = D(0, dD - 1)) != HTR_OK) return rc;
+   if ((rc = S(nz - dS, nz - 1)) != HTR_OK || (rc = S(0, dS - 1)) != HTR_OK) return rc;
+   if ((rc = finish(nz - dR, nz - 1)) != HTR_OK || (rc = finish(0, dR - 1)) != HTR_OK) return rc;
    cudaEventRecord(g_pipe.evDone, g_pipe.down);
    cudaStreamWaitEvent(st, g_pipe.evDone, 0);
    return HTR_OK;

@@ -480,3 +480,57 @@ def test_time_step(cfg, scheme, chem, kw):
             assert e <= TOL_CHEM, (step, k, e)
     # the step moved the state (the comparison is not between two copies of the initial condition)
     assert rel_err(f["Conserved"], f["Conserved_old"]) > 1e-4
+
+
+@pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "Hybrid", False, {"front": 0.3}), (CP, "SkewSymmetric", False, {}),
+                                                (AIR, "Hybrid", True, {"species_wave": 1.0, "front": 0.3, "p0": 1.0, "T0": 6.0, "U": 0.5})],
+                         ids=["constprop-hybrid", "constprop-skew", "air-hybrid-chem"])
+@pytest.mark.parametrize("nz", [16, 64, 77])
+def test_host_rhs_pipeline(cfg, scheme, chem, kw, nz):
+    """htr_host_rhs (host buffers in, Conserved_t out; z-slab pipeline with skewed stages for nz >= 60) against the same
+    task chain on resident fields, bit for bit, and against the reference tasks."""
+    import torch
+    o = oracle_for(cfg)
+    n = (24, 20, nz)
+    f = host_state(o, n, cfg, **kw)
+    s = htr.Solver(cfg)
+    # resident path: Conserved + perturbed temperature guess -> primitives, properties, sensors, RHS
+    guess = f["temperature"]*1.02
+    fl = to_device(s, f)
+    fl.upload({"temperature": guess})
+    s.UpdatePrimitiveFromConserved(fl); s.UpdatePropertiesFromPrimitive(fl)
+    if scheme == "Hybrid":
+        s.UpdateDucrosSensor(fl, 1.0)
+        for d in range(3):
+            s.UpdateShockSensor(fl, d)
+    s.UpdateDerivatives(fl, scheme, True, chem, (1.0, 0.0), 1e-3)
+    want = fl.download(["Conserved_t", "temperature"])
+    if scheme == "Hybrid":
+        sx = fl.download(["shockSensorX"])["shockSensorX"]
+        assert 0 < sx.sum() < sx.size            # both branches of the hybrid switch are live
+    for pipe in (1, 0):
+        s.set_option("pipeline", pipe)
+        hl = to_device(s, f)                     # metrics and node types resident; state fields overwritten below
+        for k in ("Conserved", "Conserved_old", "Conserved_t", "temperature", "pressure", "rho", "velocity", "MolarFracs",
+                  "MassFracs", "mu", "lam", "Di", "SoS", "DucrosSensor"):
+            hl.t[k].fill_(float("nan"))
+        hC = torch.from_numpy(f["Conserved"].copy()).pin_memory()
+        hT = torch.from_numpy(guess.copy()).pin_memory()
+        hCt = torch.full(f["Conserved"].shape, float("nan"), dtype=torch.float64).pin_memory()
+        s.HostRHS(hl, scheme, hC, hT, hCt, diffusion=True, chemistry=chem, deltaTime=1e-3)
+        torch.cuda.synchronize()
+        assert np.array_equal(hCt.numpy(), want["Conserved_t"]), (pipe, "Conserved_t")
+        assert np.array_equal(hT.numpy(), want["temperature"]), (pipe, "temperature")
+    s.set_option("pipeline", 1)
+    # and the reference chain
+    f["temperature"] = guess.copy()
+    o.update_primitive_from_conserved(f); o.update_properties_from_primitive(f)
+    _sensors(o, f, 1.0)
+    o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=1.0, RK1=0.0, dt=1e-3)
+    scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
+    if chem:
+        ref = f["Conserved_t"].copy(); f["Conserved_t"][...] = 0.0
+        o.add_chemistry_sources(f)
+        scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
+        f["Conserved_t"][...] = ref
+    assert scaled_err(hCt.numpy(), f["Conserved_t"], scale) <= (TOL_CHEM if chem else TOL_FLUX)
