@@ -111,9 +111,10 @@ def shell_rects(origin, n, h=HALO):
     return rects
 
 
-# Shell thickness per direction (x, y, z): at least the stencil reach (HALO); wider where the staged
-# kernels' tiles (32 x 8 cells in-plane, 16 planes in z: csrc/htr_fast.cuh) would otherwise run nearly empty.
-SHELL_W = (32, 8, 16)
+# Shell thickness per direction (x, y, z): at least the stencil reach (HALO), and exactly what ONE tile of the staged
+# kernels updates in that direction (csrc/htr_fast.cuh: tiles overlap by one cell per flux direction, so a 32 x 8 tile
+# updates 31 x 7 cells and the 16-plane Euler-z tile 15 planes): a shell is then one tile thick in every kernel.
+SHELL_W = (31, 7, 15)
 
 
 def boundary_rects(origin, n, w=HALO):
