@@ -107,7 +107,7 @@ def load_library(mix, variant=""):
     L.htr_rk_initialize_time_derivatives.argtypes = [vp, vp, i, vp]
     L.htr_rk_update_vars.argtypes = [i, d, i, vp, vp, vp]
     L.htr_rk_stage.argtypes = [i, d, i, vp, vp, vp]
-    L.htr_time_step.argtypes = [i, i, i, d, vp, vp, vp, d, vp]
+    L.htr_time_step.argtypes = [i, i, i, i, d, vp, vp, vp, d, vp]
     L.htr_rhs.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_rhs_parts.argtypes = [i, i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
@@ -300,10 +300,10 @@ class Solver:
                                         C.byref(fl.struct()), t, self._stream()), "htr_rk_stage")
 
     def TimeStep(self, fl, scheme, Integrator_deltaTime, diffusion=True, chemistry=False, vorticityScale=1.0,
-                 tile=None, bounds=None):
+                 tile=None, bounds=None, implicitChemistry=False):
         """One RK3 step of a block without boundary nodes (MainLoopBody, src/prometeo.rg:1348-1470)."""
         t, b = self._rects(fl, tile, bounds)
-        self._check(self.L.htr_time_step(SCHEMES[scheme], int(diffusion), int(chemistry), float(vorticityScale),
+        self._check(self.L.htr_time_step(SCHEMES[scheme], int(diffusion), int(chemistry), int(implicitChemistry), float(vorticityScale),
                                          C.byref(fl.struct()), t, b, float(Integrator_deltaTime), self._stream()), "htr_time_step")
 
     def CalculateMaxSpectralRadius(self, fl, tile=None, sync=True):

@@ -440,6 +440,7 @@ __global__ void __launch_bounds__(128) rk_initialize_time_derivatives_kernel(con
 // layout the library allocates): a row of the tile is a flat array of nx*nEq doubles and one thread moves one double,
 // so every warp access is a full 256-byte line instead of 32 spans 72 bytes apart.
 // OP 0: Conserved_old = Conserved   1: Conserved_t = 0   2: Conserved_t = -Conserved_t_old   3: UpdateVars(stage)
+//    4: Conserved_t -= Conserved_t_old (htr_time_step with implicit chemistry)
 template<int OP>
 __global__ void __launch_bounds__(256) rk_rows_kernel(const htr_fluid f, const htr_rect tile, const int stage, const double dt) {
    const int64_t e = (int64_t)blockIdx.x*256 + threadIdx.x;
@@ -448,6 +449,7 @@ __global__ void __launch_bounds__(256) rk_rows_kernel(const htr_fluid f, const h
    if (OP == 0) at<double>(f.Conserved_old, p)[e] = at<const double>(f.Conserved, p)[e];
    if (OP == 1) at<double>(f.Conserved_t, p)[e] = 0.0;
    if (OP == 2) at<double>(f.Conserved_t, p)[e] = -at<const double>(f.Conserved_t_old, p)[e];
+   if (OP == 4) at<double>(f.Conserved_t, p)[e] -= at<const double>(f.Conserved_t_old, p)[e];
    if (OP == 3) {
       const double c1 = c_rk[stage][0], c2 = c_rk[stage][1], c3 = c_rk[stage][2];
       double *C = at<double>(f.Conserved, p) + e;
@@ -1038,25 +1040,51 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
    return rc;
 }
 
-// ---- one RK3 time step of a block without boundary nodes (src/prometeo.rg:1348-1470, explicit chemistry) ---------
-// shock sensors once (Hybrid only, src/prometeo_sensor.rg:104-122), InitializeTemporaries, then per stage
-// UpdateDerivatives(RK_C[STAGE][1..2], dt*RK_C[STAGE][3]) and UpdateVars + primitive + property recovery.
-int htr_time_step(int scheme, int diffusion, int chemistry, double vorticityScale, const htr_fluid *f,
+// ---- one RK3 time step of a block without boundary nodes (MainLoopBody, src/prometeo.rg:1348-1470) ---------------
+// shock sensors once (Hybrid only, src/prometeo_sensor.rg:104-122); with implicit chemistry the operator-split
+// half step (:1360-1395: UpdateDerivatives(RK_coeffs = (0, 1), dt/2) without chemistry sources, UpdateChemistry(dt),
+// primitive/property recovery); InitializeTemporaries; then per stage UpdateDerivatives(RK_C[STAGE][1..2],
+// dt*RK_C[STAGE][3] [/2]) and UpdateVars + primitive + property recovery.  With implicit chemistry every stage's
+// Conserved_t starts from -Conserved_t_old (mkInitializeTimeDerivatives(true)); the staged kernels start from 0, so
+// Conserved_t_old is subtracted after them: same terms, the old derivative added last instead of first (rounding only).
+__global__ void __launch_bounds__(128) subtract_old_rhs_kernel(const htr_fluid f, const htr_rect tile) {
+   Pt p; if (!cellOf(p, tile)) return;
+   double *Ct = at<double>(f.Conserved_t, p);
+   const double *Cto = at<const double>(f.Conserved_t_old, p);
+   HTR_UNROLL
+   for (int i = 0; i < nEq; i++) Ct[i] -= Cto[i];
+}
+int htr_time_step(int scheme, int diffusion, int chemistry, int implicitChemistry, double vorticityScale, const htr_fluid *f,
                   const htr_rect *tile, const htr_rect *bounds, double Integrator_deltaTime, void *stream) {
    HTR_CHECK_COMMON(f, tile)
    if (!bounds) return HTR_EINVAL;
    static const double RK_C[3][3] = {{1.0, 0.0, 1.0}, {3.0/4.0, 1.0/4.0, 1.0/4.0}, {1.0/3.0, 2.0/3.0, 2.0/3.0}};
+   const double dt = Integrator_deltaTime;
    int rc;
    if (scheme == HTR_SCHEME_HYBRID) {
       if ((rc = htr_ducros_sensor(f, tile, bounds, vorticityScale, stream)) != HTR_OK) return rc;
       for (int d = 0; d < 3; d++)
          if ((rc = htr_shock_sensor(d, f, tile, bounds, stream)) != HTR_OK) return rc;
    }
+   if (implicitChemistry) {
+      if ((rc = htr_rhs(scheme, diffusion, 0, f, tile, bounds, 0.0, 1.0, dt*0.5, stream)) != HTR_OK) return rc;
+      if ((rc = htr_update_chemistry(f, tile, dt, stream)) != HTR_OK) return rc;
+      if ((rc = htr_update_primitive_from_conserved(f, tile, stream)) != HTR_OK) return rc;
+      if ((rc = htr_update_properties_from_primitive(f, tile, stream)) != HTR_OK) return rc;
+   }
    if ((rc = htr_rk_initialize_temporaries(f, tile, stream)) != HTR_OK) return rc;
    for (int stage = 1; stage <= 3; stage++) {
       const double *c = RK_C[stage - 1];
-      if ((rc = htr_rhs(scheme, diffusion, chemistry, f, tile, bounds, c[0], c[1], Integrator_deltaTime*c[2], stream)) != HTR_OK) return rc;
-      if ((rc = htr_rk_stage(stage, Integrator_deltaTime, 0, f, tile, stream)) != HTR_OK) return rc;
+      const double dts = implicitChemistry ? dt*c[2]*0.5 : dt*c[2];
+      if ((rc = htr_rhs(scheme, diffusion, chemistry && !implicitChemistry, f, tile, bounds, c[0], c[1], dts, stream)) != HTR_OK) return rc;
+      if (implicitChemistry) {
+         if (rowsContiguous({&f->Conserved_t, &f->Conserved_t_old}, *tile))
+            rk_rows_kernel<4><<<rowsGrid(*tile), 256, 0, (cudaStream_t)stream>>>(*f, *tile, 0, 0.0);
+         else
+            subtract_old_rhs_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+         if ((rc = cuerr(cudaGetLastError())) != HTR_OK) return rc;
+      }
+      if ((rc = htr_rk_stage(stage, dt, implicitChemistry, f, tile, stream)) != HTR_OK) return rc;
    }
    return HTR_OK;
 }

@@ -140,13 +140,17 @@ int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const 
  * 8 += diffusion y, x.  15 = htr_rhs.  Hybrid and SkewSymmetric schemes with the "fast" option on. */
 int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
                   const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
-/* One RK3 time step of a block without boundary nodes, explicit chemistry (MainLoopBody, src/prometeo.rg:1348-1470):
- * UpdateShockSensors (Hybrid only), InitializeTemporaries, then for STAGE = 1..3 htr_rhs with
- * RK_coeffs = RK_C[STAGE][1..2] and deltaTime*RK_C[STAGE][3] followed by htr_rk_stage.  The halo of `f`
- * (periodic wrap inside `bounds`, or ghost planes filled by the caller) must be valid for every stage: with
- * tile == bounds (one periodic block) nothing else is needed. */
-int htr_time_step(int scheme, int diffusion, int chemistry, double vorticityScale, const htr_fluid *f,
-                  const htr_rect *tile, const htr_rect *bounds, double Integrator_deltaTime, void *stream);
+/* One RK3 time step of a block without boundary nodes (MainLoopBody, src/prometeo.rg:1348-1470):
+ * UpdateShockSensors (Hybrid only); with implicitChemistry the operator-split half step (:1360-1395:
+ * UpdateDerivatives(RK_coeffs = (0, 1), deltaTime/2) without chemistry sources, UpdateChemistry(deltaTime),
+ * primitive/property recovery); InitializeTemporaries; then for STAGE = 1..3 htr_rhs with RK_coeffs = RK_C[STAGE][1..2]
+ * and deltaTime*RK_C[STAGE][3] (halved, and Conserved_t offset by -Conserved_t_old, with implicitChemistry) followed
+ * by htr_rk_stage.  `chemistry` adds the explicit source (ignored with implicitChemistry, like the reference).
+ * The halo of `f` (periodic wrap inside `bounds`, or ghost planes filled by the caller) must be valid for every
+ * stage: with tile == bounds (one periodic block) nothing else is needed. */
+int htr_time_step(int scheme, int diffusion, int chemistry, int implicitChemistry, double vorticityScale,
+                  const htr_fluid *f, const htr_rect *tile, const htr_rect *bounds, double Integrator_deltaTime,
+                  void *stream);
 
 /* ---- host-buffer stage (the call a host-resident driver binds) ----
  * h_* are HOST pointers (pinned for full copy bandwidth), dense [z][y][x][comp] over `tile`.

@@ -482,6 +482,46 @@ def test_time_step(cfg, scheme, chem, kw):
     assert rel_err(f["Conserved"], f["Conserved_old"]) > 1e-4
 
 
+def test_time_step_implicit_chemistry():
+    """htr_time_step with implicit chemistry against the reference chain (src/prometeo.rg:1360-1395 + the RK loop with
+    UseOldDerivatives): half-step RHS with RK_coeffs = (0, 1), UpdateChemistry (Rosenbrock), recovery, then three stages
+    whose Conserved_t starts from -Conserved_t_old and whose time step is halved."""
+    cfg, scheme = AIR, "Hybrid"
+    o = oracle_for(cfg)
+    f = host_state(o, (20, 14, 12), cfg, species_wave=1.0, front=0.2, p0=1.0, T0=6.0, U=0.5)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    # a quarter of the acoustic limit: with larger steps the split scheme drives trace species negative from this
+    # (far from equilibrium) state and the reference's own Rosenbrock integration returns NaN in the second step
+    dt = 0.1/o.max_spectral_radius(f)
+    names = ["Conserved", "temperature", "pressure", "velocity", "MolarFracs", "rho", "mu", "lam", "Di", "SoS", "MassFracs"]
+    for step in range(2):
+        _sensors(o, f, 1.0)
+        o.rhs(f, scheme, diffusion=True, chemistry=False, RK0=0.0, RK1=1.0, dt=0.5*dt)
+        o.update_chemistry(f, dt)                       # Conserved_t_old = Conserved_t, Conserved integrated over dt
+        o.update_primitive_from_conserved(f)
+        o.update_properties_from_primitive(f)
+        f["Conserved_old"] = f["Conserved"].copy()
+        for stage in (1, 2, 3):
+            c1, c2, c3 = RK_C[stage - 1]
+            # UpdateDerivatives with UseOldDerivatives: -Conserved_t_old, then the fluxes in task order
+            f["Conserved_t"][...] = -f["Conserved_t_old"]
+            for d in (2, 1, 0):
+                o.euler_flux(f, scheme, d, c1, c2, dt*c3*0.5)
+            for d in (2, 1, 0):
+                o.diffusion_flux(f, d)
+            f["Conserved"] = np.ascontiguousarray((c1*f["Conserved_old"] + c2*f["Conserved"]) + (c3*f["Conserved_t"])*(dt*0.5))
+            o.update_primitive_from_conserved(f)
+            o.update_properties_from_primitive(f)
+        s.TimeStep(fl, scheme, dt, diffusion=True, chemistry=True, vorticityScale=1.0, implicitChemistry=True)
+        assert s.L.htr_chemistry_failures() == 0
+        got = fl.download(names)
+        for k in names:
+            e = rel_err(got[k], f[k])
+            assert e <= 1e-8, (step, k, e)       # the adaptive Rosenbrock integrator's tolerance class (TOL = 1e-10 per step)
+    assert rel_err(f["Conserved"], f["Conserved_old"]) > 1e-5
+
+
 @pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "Hybrid", False, {"front": 0.3}), (CP, "SkewSymmetric", False, {}),
                                                 (AIR, "Hybrid", True, {"species_wave": 1.0, "front": 0.3, "p0": 1.0, "T0": 6.0, "U": 0.5})],
                          ids=["constprop-hybrid", "constprop-skew", "air-hybrid-chem"])
