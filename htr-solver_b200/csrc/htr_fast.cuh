@@ -30,7 +30,7 @@
 
 // resident CTAs per SM the register allocation aims at (tuned on B200 with ncu, see profiles/)
 #ifndef HTR_K1_MINB
-#define HTR_K1_MINB 1
+#define HTR_K1_MINB 3
 #endif
 #ifndef HTR_K2_MINB
 #define HTR_K2_MINB 3
@@ -131,7 +131,10 @@ HTR_DEV int64_t maskIndex(const RPt &c, const rbox &tile) {      // tile.lo = 0
 // Conserved_t = 0 (+ chemistry source) + Euler-z
 // block = 32 (x) x ZT_Z (z) cells of one y row; z rows overlap by one between blocks
 // ---------------------------------------------------------------------------------------------
-constexpr int ZT_X = 32, ZT_Z = 16, ZT_ROWS = ZT_Z + 5, ZT_NC = ZT_ROWS*ZT_X, ZT_NT = ZT_X*ZT_Z;
+#ifndef HTR_K1_TZ
+#define HTR_K1_TZ 8
+#endif
+constexpr int ZT_X = 32, ZT_Z = HTR_K1_TZ, ZT_ROWS = ZT_Z + 5, ZT_NC = ZT_ROWS*ZT_X, ZT_NT = ZT_X*ZT_Z;
 constexpr size_t ZT_SMEM = sizeof(double)*NV*ZT_NC + ZT_NC + ZT_NT;
 
 template<bool HYBRID, bool CHEM>

@@ -1142,9 +1142,10 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
    const int64_t nx = tile->hi[0] - tile->lo[0] + 1, ny = tile->hi[1] - tile->lo[1] + 1, nz = tile->hi[2] - tile->lo[2] + 1;
    const bool needOld = (nSpec > 1 && scheme != HTR_SCHEME_SKEWSYMMETRIC);
    const bool sensors = update_sensors && scheme == HTR_SCHEME_HYBRID;
-   // slab thickness: a multiple of the 15 planes one CTA of the Euler-z kernel updates
-   int64_t T = (nz >= 400) ? 30 : 15;
-   while ((nz + T - 1)/T > PIPE_MAXSLABS) T += 15;
+   // slab thickness: a multiple of the planes one CTA of the z kernels updates (Euler-z and diffusion-z: 7)
+   constexpr int64_t TZ = fast::ZT_Z - 1;
+   int64_t T = (nz >= 400) ? 4*TZ : 2*TZ;
+   while ((nz + T - 1)/T > PIPE_MAXSLABS) T += TZ;
    const bool pipelined = nz >= 60 && !g_no_pipe && pipeInit();
    const int ns = pipelined ? (int)((nz + T - 1)/T) : 1;
    cudaError_t e;

@@ -113,8 +113,8 @@ def shell_rects(origin, n, h=HALO):
 
 # Shell thickness per direction (x, y, z): at least the stencil reach (HALO), and exactly what ONE tile of the staged
 # kernels updates in that direction (csrc/htr_fast.cuh: tiles overlap by one cell per flux direction, so a 32 x 8 tile
-# updates 31 x 7 cells and the 16-plane Euler-z tile 15 planes): a shell is then one tile thick in every kernel.
-SHELL_W = (31, 7, 15)
+# updates 31 x 7 cells and the 8-plane z tiles 7 planes): a shell is then one tile thick in every kernel.
+SHELL_W = (31, 7, 7)
 
 
 def boundary_rects(origin, n, w=HALO):

@@ -3,7 +3,7 @@ sys.path[:0] = ['.', 'tests']
 import bench, htr_solver_b200 as htr
 from htr_solver_b200 import synthetic
 cfg = synthetic.AIRMIX_3DPERIODIC
-s = htr.Solver(cfg); n = 256
+s = htr.Solver(cfg, variant=(sys.argv[1] if len(sys.argv) > 1 else "")); n = 256
 fl = s.new_fluid(n, n, n)
 bench.fill_block(s, fl, cfg, n, (0, 0, 0), (n, n, n), 0)
 s.UpdateDucrosSensor(fl, 1.0)
