@@ -101,6 +101,7 @@ def load_library(mix, variant=""):
     L.htr_update_chemistry.argtypes = [vp, vp, d, vp]
     L.htr_update_primitive_from_conserved.argtypes = [vp, vp, vp]
     L.htr_update_properties_from_primitive.argtypes = [vp, vp, vp]
+    L.htr_update_ghost_primitive_from_conserved.argtypes = [vp, vp, vp]
     L.htr_update_conserved_from_primitive.argtypes = [vp, vp, vp]
     L.htr_max_spectral_radius.argtypes = [vp, vp, vp, vp]
     L.htr_rk_initialize_temporaries.argtypes = [vp, vp, vp]
@@ -202,6 +203,10 @@ class Fluid:
         return {n: self.interior(n).cpu().numpy() for n in (names or FIELD_NAMES)}
 
 
+# Runge-Kutta coefficients RK_C[STAGE] = (old state, current state, time derivative), src/prometeo_const.rg:54-58
+RK_C = ((1.0, 0.0, 1.0), (3.0/4.0, 1.0/4.0, 1.0/4.0), (1.0/3.0, 2.0/3.0, 2.0/3.0))
+
+
 class Solver:
     """The reference's leaf tasks for one mixture, on the current CUDA device."""
 
@@ -272,6 +277,12 @@ class Solver:
     def UpdatePropertiesFromPrimitive(self, fl, tile=None):
         t, _ = self._rects(fl, tile, None)
         self._check(self.L.htr_update_properties_from_primitive(C.byref(fl.struct()), t, self._stream()), "htr_update_properties_from_primitive")
+
+    def UpdateGhostPrimitiveFromConserved(self, fl, tile=None):
+        """Primitives of ghost copies from the exchanged (converged) temperature, no Newton iteration."""
+        t, _ = self._rects(fl, tile, None)
+        self._check(self.L.htr_update_ghost_primitive_from_conserved(C.byref(fl.struct()), t, self._stream()),
+                    "htr_update_ghost_primitive_from_conserved")
 
     def UpdateConservedFromPrimitive(self, fl, tile=None):
         t, _ = self._rects(fl, tile, None)

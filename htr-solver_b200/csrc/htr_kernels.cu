@@ -371,13 +371,18 @@ __global__ void __launch_bounds__(64) update_chemistry_kernel(const htr_fluid f,
    *at<double>(f.temperature, p) = prob.T;
 }
 
+// NEWTON = false: the temperature field already holds the converged value of these cells (ghost copies of a
+// neighbour's cells after the exchange of Conserved and temperature): every other primitive follows from it with the
+// owner's own operations, hence the owner's bits; iterating again from the converged value would move T within the
+// Newton tolerance and leave the two ranks with different ghost and owner states.
+template<bool NEWTON>
 __global__ void __launch_bounds__(128) primitive_from_conserved_kernel(const htr_fluid f, const htr_rect tile) {
    Pt p; if (!cellOf(p, tile)) return;
    double U[nEq], rho, Yi[nSpec], MixW, u[3], P;
    HTR_UNROLL
    for (int i = 0; i < nEq; i++) U[i] = ldc<double>(f.Conserved, p, i);
    double T = *at<double>(f.temperature, p);
-   primitivesFromConserved(U, rho, Yi, MixW, u, T, P);
+   primitivesFromConserved<NEWTON>(U, rho, Yi, MixW, u, T, P);
    double Xi[nSpec];
    mix::GetMolarFractions(Xi, MixW, Yi);
    double *X = at<double>(f.MolarFracs, p), *v = at<double>(f.velocity, p);
@@ -937,7 +942,12 @@ int htr_chemistry_failures(void) {
 
 int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream) {
    HTR_CHECK_COMMON(f, tile)
-   primitive_from_conserved_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   primitive_from_conserved_kernel<true><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
+   return cuerr(cudaGetLastError());
+}
+int htr_update_ghost_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   primitive_from_conserved_kernel<false><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
    return cuerr(cudaGetLastError());
 }
 int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream) {

@@ -48,6 +48,7 @@ HTR_DEV bool shockSensor(const htr_fluid &f, const Pt &p, const htr_rect &B) {
 
 // ---- variables -----------------------------------------------------------------------------
 // rho, Y, u, T, p from a conserved state; T enters as the Newton guess and leaves converged
+template<bool NEWTON = true>
 HTR_DEV void primitivesFromConserved(const double *U, double &rho, double *Yi, double &MixW, double *u,
                                      double &T, double &P) {
    double rhoYi[nSpec];
@@ -62,7 +63,7 @@ HTR_DEV void primitivesFromConserved(const double *U, double &rho, double *Yi, d
    for (int i = 0; i < 3; i++) u[i] = U[i + irU]*rhoInv;
    const double kineticEnergy = 0.5*mod2(u);
    const double e = U[irE]*rhoInv - kineticEnergy;
-   T = mix::GetTFromInternalEnergy(e, T, Yi);
+   if (NEWTON) T = mix::GetTFromInternalEnergy(e, T, Yi);      // else: T is the converged value already (ghost copies)
    P = mix::GetPFromRhoAndT(rho, MixW, T);
 }
 

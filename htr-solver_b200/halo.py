@@ -158,9 +158,36 @@ class HaloExchanger:
     def exchange_state(self):
         fl = self.fl
         exchange([fl.t["Conserved"], fl.t["temperature"]], self.n, self.rank, self.tiles, self.dist)
-        for box in self.ghost_boxes:
-            self.s.UpdatePrimitiveFromConserved(fl, tile=box)
+        for box in self.ghost_boxes:      # the owner's bits: T is the owner's converged value, no second Newton pass
+            self.s.UpdateGhostPrimitiveFromConserved(fl, tile=box)
             self.s.UpdatePropertiesFromPrimitive(fl, tile=box)
+
+    def exchange_old(self):
+        """Ghost planes of Conserved_old.  The multi-species positivity limiter of the TENO fluxes reads it at both
+        cells of a face (src/prometeo_rhs.inl, partial densities after the stage), hence in the first ghost plane:
+        call this whenever Conserved_old was set on the interior only.  initialize_temporaries() needs no message."""
+        exchange([self.fl.t["Conserved_old"]], self.n, self.rank, self.tiles, self.dist)
+
+    def initialize_temporaries(self):
+        """InitializeTemporaries (src/prometeo_rk.rg:46-56) over interior AND ghosts; the ghost planes of Conserved must
+        be current (exchange_state / sensors just ran), so Conserved_old needs no exchange of its own."""
+        self.fl.t["Conserved_old"].copy_(self.fl.t["Conserved"])
+
+    def time_step(self, scheme, Integrator_deltaTime, diffusion=True, chemistry=False, vorticityScale=1.0):
+        """One explicit RK3 step of the block (MainLoopBody, src/prometeo.rg:1348-1470; the multi-GPU form of
+        Solver.TimeStep): sensors with their exchanges, InitializeTemporaries, then per stage the overlapped
+        exchange + RHS and the fused UpdateVars + primitive/property recovery of the interior."""
+        from .core import RK_C
+        fl, s = self.fl, self.s
+        if scheme == "Hybrid":
+            self.sensors(vorticityScale)
+        else:
+            self.exchange_state()
+        self.initialize_temporaries()
+        for stage in (1, 2, 3):
+            c1, c2, c3 = RK_C[stage - 1]
+            self.rhs(scheme, diffusion, chemistry, (c1, c2), Integrator_deltaTime*c3)
+            s.UpdateVarsAndRecover(fl, stage, Integrator_deltaTime, False, tile=fl.tile())
 
     def sensors(self, vorticityScale):
         """UpdateShockSensors (src/prometeo_sensor.rg:90-124) with the two ghost exchanges it implies."""

@@ -105,6 +105,11 @@ int htr_chemistry_failures(void);
  * (src/prometeo_variables.cc:138-173, :36-86, :92-132) */
 int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream);
 int htr_update_properties_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream);
+/* UpdatePrimitiveFromConserved for ghost copies of a neighbour block's cells whose `temperature` was exchanged
+ * together with `Conserved`: pressure, velocity and MolarFracs from the converged temperature without iterating again
+ * (a second Newton pass from the converged value moves T within its 1e-8 tolerance, so ghost and owner would differ).
+ * The reference has no such task: Legion copies all fields of the ghost region (src/prometeo_partitioner.rg). */
+int htr_update_ghost_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream);
 int htr_update_conserved_from_primitive(const htr_fluid *f, const htr_rect *tile, void *stream);
 /* Runge-Kutta glue (src/prometeo_rk.rg; the reference has Regent tasks only, no C++ task to swap, so an
  * adapter registers these as new leaf tasks - INTEGRATION.md section 6).
