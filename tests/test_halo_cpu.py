@@ -100,3 +100,25 @@ def test_ghost_boxes_cover_the_ghost_region_exactly_once():
     interior = np.zeros_like(c, dtype=bool)
     interior[h:-h, h:-h, h:-h] = True
     assert np.all(c[interior] == 0) and np.all(c[~interior] == 1)
+
+
+@pytest.mark.parametrize("n", [(96, 40, 33), (64, 64, 64), (20, 18, 16)])
+def test_tile_thick_shells_tile_the_block_exactly_once(n):
+    """The shell widths the exchanger uses (one staged tile thick: SHELL_W, clipped for small blocks)."""
+    origin = (0, 64, 8)
+    w = tuple(min(halo.SHELL_W[d], max(halo.HALO, n[d] // 4)) for d in range(3))
+    assert min(w) >= halo.HALO
+    inner, shells = halo.boundary_rects(origin, n, w)
+    c = _count([inner] + shells, (n[2], n[1], n[0]), origin)
+    assert c.min() == 1 and c.max() == 1
+    # the inner box keeps the stencil reach to every block face
+    for d in range(3):
+        assert inner[0][d] - origin[d] >= halo.HALO and origin[d] + n[d] - 1 - inner[1][d] >= halo.HALO
+
+
+def test_rk_coefficients_match_the_reference():
+    """RK_C of src/prometeo_const.rg:54-58 (SSP-RK3): each stage's state weights sum to 1."""
+    from htr_solver_b200.core import RK_C
+    assert RK_C == ((1.0, 0.0, 1.0), (0.75, 0.25, 0.25), (1.0/3.0, 2.0/3.0, 2.0/3.0))
+    for a, b, _ in RK_C:
+        assert abs(a + b - 1.0) < 1e-15
