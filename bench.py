@@ -26,7 +26,12 @@ WORKLOADS = {
     "tg128_hybrid":  ("CONSTPROP_3DPERIODIC", 128, "Hybrid", True, False, "solverTests/3DPeriodic/base.json scaled to 128^3"),
     "tg128_teno":    ("CONSTPROP_3DPERIODIC", 128, "TENO", True, False, "solverTests/3DPeriodic_TENO/base.json scaled to 128^3"),
     "tg512_skew":    ("CONSTPROP_VISCOUS", 512, "SkewSymmetric", True, False, "solverTests/3DPeriodic_SkewSymmetric/base.json scaled to 512^3, Visc=5e-3"),
+    # the same AirMix box with a hot tanh temperature/pressure front (the parity tests' "air-hot-front" state): part of the
+    # faces is not smooth, so the Hybrid scheme takes the TENO branch there (config.smooth_fraction < 1)
+    "air512_front":  ("AIRMIX_3DPERIODIC", 512, "Hybrid", True, True,  "solverTests/3DPeriodic_Air/base.json scaled to 512^3 + tanh front (front=0.3, T0=6, U=0.5)"),
+    "air256_front":  ("AIRMIX_3DPERIODIC", 256, "Hybrid", True, True,  "solverTests/3DPeriodic_Air/base.json scaled to 256^3 + tanh front (front=0.3, T0=6, U=0.5)"),
 }
+IC_KW = {"air512_front": {"front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5}, "air256_front": {"front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5}}
 DEFAULT_WORKLOAD = "air512"
 
 
@@ -39,7 +44,7 @@ def algorithmic_bytes(nspec, scheme, diffusion, chemistry):
     return 8 * (neq * (2 + (1 if nspec > 1 else 0)) + nspec + 6 + 3) + 15
 
 
-def kernel_bytes(kind, nspec, scheme):
+def kernel_bytes(kind, nspec, scheme, diffusion=True):
     """Algorithmic bytes per cell of ONE launch of a per-direction kernel (fields it must read once +
     Conserved_t read-modify-write), used for the dominant-kernel roofline."""
     neq = nspec + 4
@@ -61,6 +66,14 @@ def kernel_bytes(kind, nspec, scheme):
         return 8 * (4 + 3 + 3 * nspec + 4) + 12 + 2 * 8 * neq
     if kind == "diffusion_xy":
         return 8 * (4 + 3 + 3 * nspec + 5) + 12 + 2 * 8 * neq
+    # z-marching two-pass form (csrc/htr_march.cuh)
+    if kind == "euler_z_march":     # = euler_z_chem: rho, p, velocity, Y, rhoE, T, m_e; nType, sensor; Conserved_t written
+        return 8 * (2 + 3 + nspec + 1 + 1 + 1) + 4 + (1 if scheme == "Hybrid" else 0) + 8 * neq
+    if kind == "plane_march":       # rho, p, velocity, Y, rhoE, two m_e, [mu, lam, T, Xi, Di, rhoYi, 3 m_d, 3 m_s], 3 nType, two sensors; Conserved_t RMW
+        b = 8 * (2 + 3 + nspec + 1 + 2) + 12 + (2 if scheme == "Hybrid" else 0) + 2 * 8 * neq
+        if diffusion:
+            b += 8 * (3 + 3 * nspec + 6)
+        return b
     if kind == "chem":
         return 8 * (3 + nspec) + 2 * 8 * nspec
     if kind == "zero":
@@ -106,7 +119,7 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32):
+def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32, ic_kw=None):
     """Synthetic Taylor-Green primitives generated slab by slab on the host, uploaded into the block
     (interior + halo, which for a periodic global box is just more of the same analytic field), then
     properties and conserved variables computed by the product kernels over the whole allocation."""
@@ -118,7 +131,7 @@ def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32):
     for k0 in range(0, tot, slab):
         k1 = min(tot, k0 + slab)
         f = synthetic.taylor_green((tot, tot, tot), cfg, zslab=(k0, k1), species_wave=1.0 if cfg["type"] != "ConstPropMix" else 0.0,
-                                   offset=(offset[0] - h, offset[1] - h, offset[2] - h), global_n=global_n)
+                                   offset=(offset[0] - h, offset[1] - h, offset[2] - h), global_n=global_n, **(ic_kw or {}))
         for name, arr in f.items():
             if name in fl.t:
                 fl.t[name][k0:k1].copy_(torch.from_numpy(np.ascontiguousarray(arr)))
@@ -131,7 +144,7 @@ def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32):
     torch.cuda.synchronize()
 
 
-def cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=20.0, n=None):
+def cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=20.0, n=None, ic_kw=None, keep=None):
     """Times the reference's own CPU tasks (oracle/_ref, `-O3 -fopenmp -DREALM_USE_OPENMP`, all host
     threads) on a bounded sample of the workload: the same Taylor-Green box at n^3.
     Returns (cell-updates/s, description dict).  TEST/BASELINE infrastructure only."""
@@ -149,7 +162,7 @@ def cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=20.0, n=No
     if n is None:
         n = 160 if mix != "ConstPropMix" else 192
     f = alloc_fields(n, n, n, o.nspec)
-    prim = synthetic.taylor_green(n, cfg, species_wave=1.0 if mix != "ConstPropMix" else 0.0)
+    prim = synthetic.taylor_green(n, cfg, species_wave=1.0 if mix != "ConstPropMix" else 0.0, **(ic_kw or {}))
     for k, v in prim.items():
         f[k][...] = v
     o.update_properties_from_primitive(f)
@@ -166,8 +179,55 @@ def cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=20.0, n=No
         o.rhs(f, scheme, diffusion, chemistry, 1.0, 0.0, 1e-3)
         times.append(time.perf_counter() - t0)
     best = min(times)
+    if keep is not None:
+        keep["fields"], keep["oracle"], keep["cfg"] = f, o, cfg
     return n ** 3 / best, {"kind": kind, "cores": o.threads, "sample": f"{n}^3 box of the same workload, best of {len(times)} RHS evaluations after 1 warm-up",
                            "host_cpus": os.cpu_count(), "ms_per_rhs": best * 1e3, "n": n}
+
+
+def sample_parity(solver, keep, scheme, diffusion, chemistry):
+    """The GPU path (htr_rhs resident and htr_host_rhs from host buffers) on the SAME sample box the CPU baseline just
+    evaluated with the reference's own tasks: max error of Conserved_t relative to the flux-operand scale
+    (tests/parity.py), relative to max|ref| per component (what scripts/compare_hdf.py + solverTests/testAll.py use), and
+    the number of shock-sensor decisions that differ."""
+    import torch
+    from parity import euler_scale, scaled_err, rel_err
+    f, o = keep["fields"], keep["oracle"]
+    ref = f["Conserved_t"].copy()
+    nz, ny, nx = f["rho"].shape
+    fl = solver.new_fluid(nx, ny, nz)
+    fl.upload({k: v for k, v in f.items() if k != "Conserved_t"})
+    flips = 0
+    if scheme == "Hybrid":
+        keep_s = {k: f[k].copy() for k in ("shockSensorX", "shockSensorY", "shockSensorZ")}
+        solver.UpdateDucrosSensor(fl, 1.0)
+        for d in range(3):
+            solver.UpdateShockSensor(fl, d)
+        got_s = fl.download(list(keep_s))
+        flips = int(sum((got_s[k] != keep_s[k]).sum() for k in keep_s))
+        fl.upload(keep_s)                      # same decisions for the flux comparison
+    solver.UpdateDerivatives(fl, scheme, diffusion, chemistry, (1.0, 0.0), 1e-3)
+    got = fl.download(["Conserved_t"])["Conserved_t"]
+    scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
+    if chemistry:
+        f["Conserved_t"][...] = 0.0
+        o.add_chemistry_sources(f)
+        scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
+        f["Conserved_t"][...] = ref
+    out = {"sample_grid": [nx, ny, nz], "max_scaled_err": scaled_err(got, ref, scale), "max_rel_err_by_maxref": rel_err(got, ref),
+           "sensor_flips": flips, "tolerance": 1e-10 if chemistry else 1e-12,
+           "against": "the reference's CPU tasks (oracle/_ref, -O3 -fopenmp build) on the same inputs"}
+    # the host-buffer entry point on the same sample
+    neq = got.shape[-1]
+    hC = torch.from_numpy(np.ascontiguousarray(f["Conserved"])).pin_memory()
+    hT = torch.from_numpy(np.ascontiguousarray(f["temperature"])).pin_memory()
+    hCt = torch.empty((nz, ny, nx, neq), dtype=torch.float64).pin_memory()
+    solver.HostRHS(fl, scheme, hC, hT, hCt, diffusion=diffusion, chemistry=chemistry, deltaTime=1e-3)
+    torch.cuda.synchronize()
+    out["host_rhs_max_scaled_err"] = scaled_err(hCt.numpy(), ref, scale)
+    out["ok"] = bool(out["max_scaled_err"] <= out["tolerance"] and out["host_rhs_max_scaled_err"] <= out["tolerance"])
+    del fl
+    return out
 
 
 def run_reference(args, rank, world):
@@ -177,7 +237,7 @@ def run_reference(args, rank, world):
         return
     # each "step" = one RHS evaluation of the bounded sample; steps/warmup are honoured on the sample
     from oracle_lib import Oracle  # noqa: F401
-    val, desc = cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=max(5.0, min(60.0, 4.0 * args.steps)))
+    val, desc = cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=max(5.0, min(60.0, 4.0 * args.steps)), ic_kw=IC_KW.get(name))
     line = {"impl": "reference", "metric": "fp64 RHS cell-updates/s", "value": val, "unit": "cell-updates/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": desc["ms_per_rhs"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -232,12 +292,12 @@ def run_gpu(args, rank, world, local_rank):
     if world == 1:
         # one tile = the whole periodic box: no ghost cells, stencils wrap by index like the reference
         fl = solver.new_fluid(n, n, n, halo=0, origin=origin)
-        fill_block(solver, fl, cfg, n, origin, gN, 0)
+        fill_block(solver, fl, cfg, n, origin, gN, 0, ic_kw=IC_KW.get(name))
         tile, bounds = fl.tile(), fl.tile()
     else:
         from htr_solver_b200 import halo as halo_mod
         fl = solver.new_fluid(n, n, n, halo=halo_mod.HALO, origin=origin)
-        fill_block(solver, fl, cfg, n, origin, gN, halo_mod.HALO)
+        fill_block(solver, fl, cfg, n, origin, gN, halo_mod.HALO, ic_kw=IC_KW.get(name))
         exchanger = halo_mod.HaloExchanger(solver, fl, tiles, tc, rank, world)
         tile = fl.tile()
         bounds = htr.Rect.make((-2 ** 40,) * 3, (2 ** 40,) * 3)     # ghosts are resident: never wrap
@@ -289,6 +349,7 @@ def run_gpu(args, rank, world, local_rank):
     # htr_rhs_parts runs one staged kernel (+ its masked generic pass, a few microseconds when nothing is deferred)
     kern = {}
     staged = scheme in ("Hybrid", "SkewSymmetric")
+    march = staged and not any(kv.replace(" ", "") == "march=0" for kv in args.opt)
     if rank == 0:
         def timed(label, fn, reps=5):
             ts = []
@@ -297,8 +358,11 @@ def run_gpu(args, rank, world, local_rank):
                 a.record(); fn(); b.record(); torch.cuda.synchronize()
                 ts.append(a.elapsed_time(b))
             kern[label] = float(np.mean(ts[1:]))
-        if staged:
+        if staged and march:
+            parts = [("euler_z_march", 1), ("plane_march", 2)]
+        elif staged:
             parts = [("euler_z_chem", 1), ("euler_xy", 2)] + ([("diffusion_z", 4), ("diffusion_xy", 8)] if diffusion else [])
+        if staged:
             for label, m in parts:
                 timed(label, lambda m=m: solver.UpdateDerivativesParts(m, fl, scheme, diffusion, chemistry, (1.0, 0.0), 1e-3, tile=tile, bounds=bounds))
         else:
@@ -318,7 +382,7 @@ def run_gpu(args, rank, world, local_rank):
         try:
             hl = fl if world == 1 else solver.new_fluid(n, n, n, halo=0, origin=(0, 0, 0))
             if world > 1:      # e2e at N>1: every rank drives its own periodic block through the host API
-                fill_block(solver, hl, cfg, n, (0, 0, 0), (n, n, n), 0)
+                fill_block(solver, hl, cfg, n, (0, 0, 0), (n, n, n), 0, ic_kw=IC_KW.get(name))
             hC = torch.empty((n, n, n, neq), dtype=torch.float64).pin_memory()
             hT = torch.empty((n, n, n), dtype=torch.float64).pin_memory()
             hCt = torch.empty((n, n, n, neq), dtype=torch.float64).pin_memory()
@@ -404,12 +468,12 @@ def run_gpu(args, rank, world, local_rank):
     if kern:
         top = max(kern, key=kern.get)
         kind = top if staged else (top.split("_")[0] if not top.startswith("chem") else "chem")
-        kb = kernel_bytes(kind, nspec, scheme)
+        kb = kernel_bytes(kind, nspec, scheme, diffusion)
         ach = kb * cells_rank / (kern[top] * 1e-3) / 1e9
         B = algorithmic_bytes(nspec, scheme, diffusion, chemistry)
         # measured DRAM bytes of that kernel (ncu --set full capture committed under profiles/), per launch
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "r1_dram_traffic.json")
+        tpath = os.path.join(ROOT, "profiles", "r2_dram_traffic.json" if march else "r1_dram_traffic.json")
         if os.path.exists(tpath):
             t = json.load(open(tpath)).get(cfg["type"], {}).get(top)
             if t:
@@ -419,18 +483,33 @@ def run_gpu(args, rank, world, local_rank):
                 "kernels_ms": kern, "rhs_bytes_per_cell": B,
                 "rhs_achieved_gbs": B * cells_rank * world * args.steps / (ms * 1e-3) / 1e9 / world,
                 "rhs_frac": B * cells_rank * args.steps / (ms * 1e-3) / 1e9 / peak}
-    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry)
+    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry, march=march)
     if exchanger is not None:
         launches_per_step = exchanger.launches_per_step(diffusion, chemistry, scheme)
 
+    # fp64 pipe peak of this device (DFMA chains, csrc/htr_kernels.cu: htr_probe_fp64): the other roofline of the path
+    if roof is not None:
+        try:
+            import ctypes
+            tf = (ctypes.c_double * 2)()
+            solver.L.htr_probe_fp64.argtypes = [ctypes.c_double, ctypes.c_void_p, ctypes.c_void_p]
+            if solver.L.htr_probe_fp64(1.5, tf, solver._stream()) == 0:
+                roof["fp64_peak_tflops"] = {"sustained": tf[0], "burst": tf[1], "how": "16 independent DFMA chains per thread, 8 CTAs x 256 threads per SM, CUDA events"}
+        except Exception as ex:
+            roof["fp64_peak_tflops"] = {"error": repr(ex)[:120]}
+
     cpu = None
+    parity = None
     if world == 1 and not args.no_cpu:
         try:
-            v, desc = cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=args.cpu_budget)
+            keep = {}
+            v, desc = cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=args.cpu_budget, ic_kw=IC_KW.get(name), keep=keep)
             cpu = {"value": v, "unit": "cell-updates/s", "cores": desc["cores"], "kind": desc["kind"], "sample": desc["sample"],
                    "host_cpus": desc["host_cpus"]}
+            parity = sample_parity(solver, keep, scheme, diffusion, chemistry)
         except Exception as ex:
-            cpu = {"value": None, "unit": "cell-updates/s", "error": repr(ex)[:200]}
+            cpu = cpu or {"value": None, "unit": "cell-updates/s", "error": repr(ex)[:200]}
+            parity = parity or {"error": repr(ex)[:200]}
 
     line = {"metric": "fp64 RHS cell-updates/s", "value": value, "unit": "cell-updates/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True,
@@ -440,7 +519,7 @@ def run_gpu(args, rank, world, local_rank):
                        "smooth_fraction": smooth, "l2": "inputs larger than L2 (no flush needed)" if n >= 128 else "inputs may fit L2",
                        "halo": "none (periodic wrap by index)" if world == 1 else "3 ghost planes, NCCL send/recv per step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-            "roofline": roof, "cpu_baseline": cpu, "time_step": tstep, "build": solver.L.htr_build_info().decode()}
+            "roofline": roof, "cpu_baseline": cpu, "parity": parity, "time_step": tstep, "build": solver.L.htr_build_info().decode()}
     emit(json.dumps(line))
 
 

@@ -57,8 +57,11 @@ def ncomp(c, nspec):
     return {0: 1, 3: 3, "S": nspec, "E": nspec + 4}[c]
 
 
-def rhs_launches(scheme, diffusion, chemistry, fast=True):
+def rhs_launches(scheme, diffusion, chemistry, fast=True, march=True):
     """Kernels one htr_rhs call launches (csrc/htr_kernels.cu: htr_rhs)."""
+    if fast and march and scheme in ("Hybrid", "SkewSymmetric"):
+        # Euler-z march + its masked pass; plane march + masked Euler y, x (+ masked diffusion z, y, x)
+        return 2 + 3 + (3 if diffusion else 0)
     if fast and scheme in ("Hybrid", "SkewSymmetric"):
         return 5 + (5 if diffusion else 0)       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked
     return 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
@@ -112,6 +115,7 @@ def load_library(mix, variant=""):
     L.htr_rhs.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_rhs_parts.argtypes = [i, i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
+    L.htr_probe_fp64.argtypes = [d, vp, vp]
     assert L.htr_mixture_name().decode() == mix
     _LIBS[key] = L
     return L

@@ -20,6 +20,7 @@
 #include "htr_fast.cuh"
 #include "htr_fast_bulk.cuh"
 #include "htr_diff_bulk.cuh"
+#include "htr_march.cuh"
 
 namespace htr {
 
@@ -317,6 +318,110 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
       if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+   }
+   return cudaSuccess;
+}
+
+// ---- z-marching two-pass form (htr_march.cuh) ---------------------------------------------------
+static bool g_no_march = false;         // htr_set_option("march", 0): the four staged kernels of htr_fast.cuh instead
+static int g_march_kz = 64;             // planes per CTA of euler_z_march_kernel   ("march_kz")
+static int g_march_kp = 32;             // planes per CTA of plane_march_kernel     ("march_kp")
+
+// Uniform-layout view: every field the kernels read is x-dense and all share one cell pitch in y and in z
+// (what one Legion instance per tile gives, src/prometeo_mapper.cc:1142-1204).  false -> htr_fast.cuh path.
+static bool makeUniform(const rfluid &rf, const rbox &rt, const rbox &rb, bool hybrid, bool chem, bool diffusion, march::UF &u) {
+   int64_t SY = -1, SZ = -1;
+   auto ok = [&](const racc &a, int elem, int ncomp) -> bool {
+      if (!a.base || ((uintptr_t)a.base & (uintptr_t)(elem - 1))) return false;
+      const int64_t cs = (int64_t)elem*ncomp;
+      if (a.s[0] != cs || a.s[1] % cs || a.s[2] % cs) return false;
+      const int64_t sy = a.s[1]/cs, sz = a.s[2]/cs;
+      if (SY < 0) { SY = sy; SZ = sz; }
+      return sy == SY && sz == SZ && sy > 0 && sz > 0;
+   };
+   #define HTR_UD(dst, src, nc) if (!ok(rf.src, 8, nc)) return false; u.dst = reinterpret_cast<double*>(rf.src.base);
+   HTR_UD(rho, rho, 1) HTR_UD(p, pressure, 1) HTR_UD(Y, MassFracs, nSpec) HTR_UD(vel, velocity, 3) HTR_UD(C, Conserved, nEq)
+   if (!ok(rf.Conserved_t, 8, nEq)) return false;
+   u.Ct = reinterpret_cast<double*>(rf.Conserved_t.base);
+   HTR_UD(me[0], dcsi_e, 1) HTR_UD(me[1], deta_e, 1) HTR_UD(me[2], dzet_e, 1)
+   u.T = u.mu = u.lam = u.X = u.Di = nullptr;
+   for (int d = 0; d < 3; d++) { u.md[d] = u.ms[d] = nullptr; u.sens[d] = nullptr; }
+   if (chem || diffusion) { HTR_UD(T, temperature, 1) }
+   if (diffusion) {
+      HTR_UD(mu, mu, 1) HTR_UD(lam, lam, 1) HTR_UD(X, MolarFracs, nSpec) HTR_UD(Di, Di, nSpec)
+      HTR_UD(md[0], dcsi_d, 1) HTR_UD(md[1], deta_d, 1) HTR_UD(md[2], dzet_d, 1)
+      HTR_UD(ms[0], dcsi_s, 1) HTR_UD(ms[1], deta_s, 1) HTR_UD(ms[2], dzet_s, 1)
+   }
+   #undef HTR_UD
+   const racc *nt[3] = {&rf.nType_x, &rf.nType_y, &rf.nType_z};
+   const racc *ss[3] = {&rf.shockSensorX, &rf.shockSensorY, &rf.shockSensorZ};
+   for (int d = 0; d < 3; d++) {
+      if (!ok(*nt[d], 4, 1)) return false;
+      u.nT[d] = reinterpret_cast<const int*>(nt[d]->base);
+      if (hybrid) {
+         if (!ok(*ss[d], 1, 1)) return false;
+         u.sens[d] = reinterpret_cast<const uint8_t*>(ss[d]->base);
+      }
+   }
+   if (SY >= ((int64_t)1 << 24) || SZ >= ((int64_t)1 << 40)) return false;
+   u.SY = (int)SY;
+   if (SZ >= ((int64_t)1 << 31)) return false;
+   u.SZ = (int)SZ;
+   int64_t ext[3];                        // largest |coordinate| a (wrapped) stencil point can have, per direction
+   for (int d = 0; d < 3; d++) {
+      u.n[d] = rt.hi[d] + 1;
+      u.blo[d] = rb.lo[d]; u.bhi[d] = rb.hi[d];
+      // a stencil point overshoots the box by at most 3 cells: the single-step wrap needs a box at least that wide
+      if ((int64_t)rb.hi[d] - rb.lo[d] + 1 < 8) return false;
+      const int64_t BIG = (int64_t)1 << 29;
+      const int64_t lo = (rb.lo[d] > -BIG && rb.lo[d] < -3) ? rb.lo[d] : -3;
+      const int64_t hi = (rb.hi[d] < BIG && rb.hi[d] > rt.hi[d] + 3) ? rb.hi[d] : rt.hi[d] + 3;
+      ext[d] = (-lo > hi ? -lo : hi) + 64;
+   }
+   // the kernels index cells with 32 bits
+   if (ext[0] + ext[1]*SY + ext[2]*SZ >= ((int64_t)1 << 31)) return false;
+   return true;
+}
+
+template<int SCHEME>
+static cudaError_t launchMarch(bool chem, bool diffusion, const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
+                               const march::UF &u, const EulerParams &ep, uint8_t *scratch, cudaStream_t st, int parts) {
+   constexpr bool HY = (SCHEME == HTR_SCHEME_HYBRID);
+   const int64_t n[3] = {u.n[0], u.n[1], u.n[2]};
+   int *flags = reinterpret_cast<int*>(scratch);      // cells deferred by: [0] Euler z pass, [1] plane pass
+   uint8_t *maskZ = scratch + 16, *maskP = maskZ + n[0]*n[1]*n[2];
+   cudaError_t e;
+   if ((e = cudaMemsetAsync(flags, 0, 16, st)) != cudaSuccess) return e;
+   static bool attr = false;
+   if (!attr) {
+      cudaFuncSetAttribute(march::plane_march_kernel<HY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march::PM_SMEM);
+      cudaFuncSetAttribute(march::plane_march_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march::PM_SMEM);
+      attr = true;
+   }
+   if (parts & PART_EZ) {
+      int kch = g_march_kz < 6 ? 6 : g_march_kz;
+      dim3 grid((unsigned)((n[0] + 31)/32), (unsigned)((n[1] + march::MZ_TY - 1)/march::MZ_TY), (unsigned)((n[2] + kch - 1)/kch));
+      dim3 block(32, march::MZ_TY, 1);
+      if (chem) march::euler_z_march_kernel<HY, true><<<grid, block, 0, st>>>(u, maskZ, flags, kch);
+      else      march::euler_z_march_kernel<HY, false><<<grid, block, 0, st>>>(u, maskZ, flags, kch);
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      if ((e = launchMasked<2, FLUX_EULER, SCHEME>(f, tile, B, ep, maskZ, flags, st)) != cudaSuccess) return e;
+   }
+   if (parts & PART_EXY) {
+      int kch = g_march_kp < 1 ? 1 : g_march_kp;
+      dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + 6)/7), (unsigned)((n[2] + kch - 1)/kch));
+      dim3 block(32, 8, 1);
+      if (diffusion) march::plane_march_kernel<HY, true><<<grid, block, march::PM_SMEM, st>>>(u, maskP, flags + 1, kch);
+      else           march::plane_march_kernel<HY, false><<<grid, block, march::PM_SMEM, st>>>(u, maskP, flags + 1, kch);
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st)) != cudaSuccess) return e;
+      if (diffusion) {
+         const EulerParams e0 = {0, 0, 0};
+         if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st)) != cudaSuccess) return e;
+         if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st)) != cudaSuccess) return e;
+         if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st)) != cudaSuccess) return e;
+      }
    }
    return cudaSuccess;
 }
@@ -776,6 +881,9 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
+   if (strcmp(name, "march") == 0) { g_no_march = (value == 0); return HTR_OK; }
+   if (strcmp(name, "march_kz") == 0) { if (value < 1) return HTR_EINVAL; g_march_kz = value; return HTR_OK; }
+   if (strcmp(name, "march_kp") == 0) { if (value < 1) return HTR_EINVAL; g_march_kp = value; return HTR_OK; }
    return HTR_EINVAL;
 }
 
@@ -940,6 +1048,55 @@ int htr_chemistry_failures(void) {
    return n;
 }
 
+// ---- fp64 pipe probe: the denominator of the fp64 roofline -----------------------
+// Every thread runs 16 independent DFMA chains; 2 flops per DFMA.  Timed with CUDA events on `stream`.
+__global__ void __launch_bounds__(256) fp64_probe_kernel(double *out, const int iters, const double a, const double b) {
+   double v[16];
+   HTR_UNROLL
+   for (int k = 0; k < 16; k++) v[k] = a + k + threadIdx.x*1e-3;
+   for (int it = 0; it < iters; it++) {
+      HTR_UNROLL
+      for (int k = 0; k < 16; k++) v[k] = fma(v[k], a, b);
+   }
+   double sacc = 0.0;
+   HTR_UNROLL
+   for (int k = 0; k < 16; k++) sacc += v[k];
+   if (sacc == 123.456) out[0] = sacc;       // never true: keeps the chains alive
+}
+int htr_probe_fp64(double seconds, double *tflops, void *stream) {
+   if (!tflops) return HTR_EINVAL;
+   cudaStream_t st = (cudaStream_t)stream;
+   int dev = 0, sms = 148;
+   cudaGetDevice(&dev);
+   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+   double *d = nullptr;
+   if (cudaMalloc(&d, 8) != cudaSuccess) return 1000 + (int)cudaErrorMemoryAllocation;
+   cudaEvent_t e0, e1;
+   cudaEventCreate(&e0); cudaEventCreate(&e1);
+   const int blocks = sms*8, iters = 4096;
+   const double flopsPerLaunch = 2.0*16*iters*256.0*blocks;
+   fp64_probe_kernel<<<blocks, 256, 0, st>>>(d, iters, 0.999999, 1e-9);      // warm-up
+   cudaStreamSynchronize(st);
+   double best = 0.0, elapsed = 0.0;
+   int launches = 0;
+   while (elapsed < seconds*1e3 || launches < 3) {
+      cudaEventRecord(e0, st);
+      for (int r = 0; r < 20; r++) fp64_probe_kernel<<<blocks, 256, 0, st>>>(d, iters, 0.999999, 1e-9);
+      cudaEventRecord(e1, st);
+      if (cudaEventSynchronize(e1) != cudaSuccess) break;
+      float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+      elapsed += ms; launches++;
+      const double tf = 20*flopsPerLaunch/(ms*1e-3)/1e12;
+      tflops[0] = tf;                           // sustained: the last batch
+      if (tf > best) best = tf;
+      if (launches > 2000) break;
+   }
+   tflops[1] = best;                            // burst: the best batch
+   cudaEventDestroy(e0); cudaEventDestroy(e1);
+   cudaFree(d);
+   return cuerr(cudaGetLastError());
+}
+
 int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream) {
    HTR_CHECK_COMMON(f, tile)
    primitive_from_conserved_kernel<true><<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile);
@@ -1027,6 +1184,14 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
       uint8_t *scratch = (uint8_t*)scratchFor((size_t)(2*cells + 16), st);
       if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
       const EulerParams ep = {RK0, RK1, deltaTime};
+      march::UF u;
+      if (!g_no_march && makeUniform(rf, rt, rb, scheme == HTR_SCHEME_HYBRID, chemistry != 0, diffusion != 0, u)) {
+         // two passes over Conserved_t (htr_march.cuh); parts: PART_EZ = Euler-z pass, PART_EXY = plane pass
+         const cudaError_t em = (scheme == HTR_SCHEME_HYBRID)
+            ? launchMarch<HTR_SCHEME_HYBRID>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, parts)
+            : launchMarch<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, parts);
+         return cuerr(em);
+      }
       cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
          ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts)
          : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts);

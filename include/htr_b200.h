@@ -101,6 +101,11 @@ int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double Integr
 /* Cells whose implicit integration hit the step/iteration caps since the last call (the reference
  * asserts there, src/Utils/math_utils.hpp:233,240).  Synchronises the device and resets the counter. */
 int htr_chemistry_failures(void);
+
+/* fp64 pipe probe (measurement only): runs independent DFMA chains for about `seconds` on the current device and
+ * returns the sustained (tflops[0], last batch) and burst (tflops[1], best batch) DFMA rate in TFLOP/s: the
+ * denominator of the fp64 roofline of the chemistry / TENO kernels. */
+int htr_probe_fp64(double seconds, double *tflops, void *stream);
 /* UpdatePrimitiveFromConservedTask / UpdatePropertiesFromPrimitiveTask / UpdateConservedFromPrimitiveTask
  * (src/prometeo_variables.cc:138-173, :36-86, :92-132) */
 int htr_update_primitive_from_conserved(const htr_fluid *f, const htr_rect *tile, void *stream);

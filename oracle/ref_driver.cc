@@ -251,6 +251,14 @@ int htr_oracle_max_threads(void) {
 #endif
 }
 
+void htr_oracle_set_threads(int n) {
+#ifdef _OPENMP
+   if (n > 0) omp_set_num_threads(n);       // overrides an inherited OMP_NUM_THREADS=1 (torchrun sets it)
+#else
+   (void)n;
+#endif
+}
+
 int htr_oracle_init_constprop(double gasConstant, double gamma, double prandtl,
                               int visc_model, double p0, double p1, double p2) {
 #ifdef HTR_EOS_IS_CONSTPROP

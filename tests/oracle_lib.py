@@ -91,6 +91,14 @@ class Oracle:
         self.nspec = L.htr_oracle_nspec()
         self.neq = L.htr_oracle_neq()
         self.threads = L.htr_oracle_max_threads()
+        if omp and hasattr(L, "htr_oracle_set_threads"):
+            # all host cores this process may use, whatever OMP_NUM_THREADS it inherited (torchrun exports 1)
+            try:
+                ncpu = len(os.sched_getaffinity(0))
+            except AttributeError:
+                ncpu = os.cpu_count() or 1
+            L.htr_oracle_set_threads(C.c_int(ncpu))
+            self.threads = L.htr_oracle_max_threads()
         assert self.mixture == mix
 
     # ---- mixture ----

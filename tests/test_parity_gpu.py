@@ -244,13 +244,17 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
     fl = to_device(s, f)
     out = {}
     try:
-        for fast in (1, 0):
+        # 1: the two-pass z-marching kernels (csrc/htr_march.cuh, the default); 2: the four staged kernels of
+        # csrc/htr_fast.cuh ("march" = 0); 0: the per-task kernels ("fast" = 0)
+        for path, (fast, march) in {1: (1, 1), 2: (1, 0), 0: (0, 0)}.items():
             s.set_option("fast", fast)
+            s.set_option("march", march)
             fl.t["Conserved_t"].fill_(-3.0)
             s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=(0.75, 0.25), deltaTime=1e-3)
-            out[fast] = fl.download(["Conserved_t"])["Conserved_t"]
+            out[path] = fl.download(["Conserved_t"])["Conserved_t"]
     finally:
         s.set_option("fast", 1)
+        s.set_option("march", 1)
     o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=0.75, RK1=0.25, dt=1e-3)
     scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
     if chem:
@@ -261,9 +265,41 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         f["Conserved_t"][...] = ref
     if variant == "strict":
         assert np.array_equal(out[1], out[0])
+        assert np.array_equal(out[2], out[0])
     else:
         assert scaled_err(out[1], out[0], scale) <= TOL_FLUX
+        assert scaled_err(out[2], out[0], scale) <= TOL_FLUX
     assert scaled_err(out[1], f["Conserved_t"], scale) <= (TOL_CHEM if chem else TOL_FLUX)
+
+
+@pytest.mark.parametrize("cfg,chem,kw", [(CP, False, {"front": 0.3, "stretch": 0.2}),
+                                         (AIR, True, {"species_wave": 1.0, "front": 0.3, "stretch": 0.1})], ids=["constprop", "air"])
+@pytest.mark.parametrize("diffusion", [True, False], ids=["diff", "nodiff"])
+@pytest.mark.parametrize("kz,kp", [(64, 32), (7, 5)], ids=["long", "short-chunks"])
+def test_march_rhs_equals_per_task_sequence(cfg, chem, kw, diffusion, kz, kp):
+    """The z-marching kernels (csrc/htr_march.cuh) on a periodic box with several tiles and z chunks per direction
+    (70 x 37 x 41: partial tiles in x and y, chunk seams in z, wrap in all directions) and a mixed sensor field,
+    with and without the diffusion phase, strict build: bit-identical with the per-task sequence."""
+    o = oracle_for(cfg)
+    n = (70, 37, 41)
+    f = host_state(o, n, cfg, **kw)
+    _sensors(o, f)
+    f["shockSensorX"][:, :, 7::11] = 0; f["shockSensorY"][:, 5::9, :] = 0; f["shockSensorZ"][3::8, :, :] = 0
+    s = htr.Solver(cfg, variant="strict")
+    fl = to_device(s, f)
+    out = {}
+    try:
+        s.set_option("march_kz", kz); s.set_option("march_kp", kp)
+        for fast in (1, 0):
+            s.set_option("fast", fast)
+            fl.t["Conserved_t"].fill_(-3.0)
+            s.UpdateDerivatives(fl, "Hybrid", diffusion=diffusion, chemistry=chem, RK_coeffs=(0.75, 0.25), deltaTime=1e-3)
+            out[fast] = fl.download(["Conserved_t"])["Conserved_t"]
+    finally:
+        s.set_option("fast", 1); s.set_option("march_kz", 64); s.set_option("march_kp", 32)
+    assert np.isfinite(out[1]).all()
+    bad = np.argwhere(out[1] != out[0])
+    assert bad.size == 0, (len(bad), bad[:5].tolist())
 
 
 @pytest.mark.parametrize("cfg,chem,kw", [(AIR, True, {"species_wave": 1.0, "front": 0.3})], ids=["air"])
