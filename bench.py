@@ -349,7 +349,10 @@ def run_gpu(args, rank, world, local_rank):
     # htr_rhs_parts runs one staged kernel (+ its masked generic pass, a few microseconds when nothing is deferred)
     kern = {}
     staged = scheme in ("Hybrid", "SkewSymmetric")
-    march = staged and not any(kv.replace(" ", "") == "march=0" for kv in args.opt)
+    march = 1 if staged else 0          # library default (htr_set_option "march"): bit 0 Euler-z march, bit 1 plane march
+    for kv in args.opt:
+        if staged and kv.replace(" ", "").startswith("march="):
+            march = int(kv.split("=")[1])
     if rank == 0:
         def timed(label, fn, reps=5):
             ts = []
@@ -358,10 +361,10 @@ def run_gpu(args, rank, world, local_rank):
                 a.record(); fn(); b.record(); torch.cuda.synchronize()
                 ts.append(a.elapsed_time(b))
             kern[label] = float(np.mean(ts[1:]))
-        if staged and march:
+        if staged and (march & 2):
             parts = [("euler_z_march", 1), ("plane_march", 2)]
         elif staged:
-            parts = [("euler_z_chem", 1), ("euler_xy", 2)] + ([("diffusion_z", 4), ("diffusion_xy", 8)] if diffusion else [])
+            parts = [("euler_z_march" if march & 1 else "euler_z_chem", 1), ("euler_xy", 2)] + ([("diffusion_z", 4), ("diffusion_xy", 8)] if diffusion else [])
         if staged:
             for label, m in parts:
                 timed(label, lambda m=m: solver.UpdateDerivativesParts(m, fl, scheme, diffusion, chemistry, (1.0, 0.0), 1e-3, tile=tile, bounds=bounds))
@@ -473,7 +476,9 @@ def run_gpu(args, rank, world, local_rank):
         B = algorithmic_bytes(nspec, scheme, diffusion, chemistry)
         # measured DRAM bytes of that kernel (ncu --set full capture committed under profiles/), per launch
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "r2_dram_traffic.json" if march else "r1_dram_traffic.json")
+        tpath = os.path.join(ROOT, "profiles", "r2_dram_traffic.json")
+        if not os.path.exists(tpath):
+            tpath = os.path.join(ROOT, "profiles", "r1_dram_traffic.json")
         if os.path.exists(tpath):
             t = json.load(open(tpath)).get(cfg["type"], {}).get(top)
             if t:
@@ -483,7 +488,7 @@ def run_gpu(args, rank, world, local_rank):
                 "kernels_ms": kern, "rhs_bytes_per_cell": B,
                 "rhs_achieved_gbs": B * cells_rank * world * args.steps / (ms * 1e-3) / 1e9 / world,
                 "rhs_frac": B * cells_rank * args.steps / (ms * 1e-3) / 1e9 / peak}
-    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry, march=march)
+    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry, march=bool(march & 2))
     if exchanger is not None:
         launches_per_step = exchanger.launches_per_step(diffusion, chemistry, scheme)
 

@@ -323,7 +323,11 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
 }
 
 // ---- z-marching two-pass form (htr_march.cuh) ---------------------------------------------------
-static bool g_no_march = false;         // htr_set_option("march", 0): the four staged kernels of htr_fast.cuh instead
+// htr_set_option("march", m): bit 0 = euler_z_march_kernel instead of fast::euler_z_chem_kernel, bit 1 = plane_march_kernel
+// instead of the three staged kernels euler_xy / diffusion_z / diffusion_xy.  Default 1: measured on B200 at 512^3 AirMix
+// (profiles/r2_*): Euler-z march 14.4 ms vs 15.7 ms staged; plane march 60.5 ms vs 13.5 + 13.6 + 23.0 ms staged (16 warps per
+// SM at 112 KB of shared memory per CTA leave its load latency exposed: issue slots 25 % busy vs 36-45 %).
+static int g_march = 1;
 static int g_march_kz = 64;             // planes per CTA of euler_z_march_kernel   ("march_kz")
 static int g_march_kp = 32;             // planes per CTA of plane_march_kernel     ("march_kp")
 
@@ -881,7 +885,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
-   if (strcmp(name, "march") == 0) { g_no_march = (value == 0); return HTR_OK; }
+   if (strcmp(name, "march") == 0) { if (value < 0 || value > 3) return HTR_EINVAL; g_march = value; return HTR_OK; }
    if (strcmp(name, "march_kz") == 0) { if (value < 1) return HTR_EINVAL; g_march_kz = value; return HTR_OK; }
    if (strcmp(name, "march_kp") == 0) { if (value < 1) return HTR_EINVAL; g_march_kp = value; return HTR_OK; }
    return HTR_EINVAL;
@@ -1185,12 +1189,14 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
       if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
       const EulerParams ep = {RK0, RK1, deltaTime};
       march::UF u;
-      if (!g_no_march && makeUniform(rf, rt, rb, scheme == HTR_SCHEME_HYBRID, chemistry != 0, diffusion != 0, u)) {
-         // two passes over Conserved_t (htr_march.cuh); parts: PART_EZ = Euler-z pass, PART_EXY = plane pass
+      if (g_march && makeUniform(rf, rt, rb, scheme == HTR_SCHEME_HYBRID, chemistry != 0, diffusion != 0, u)) {
+         // z-marching kernels (htr_march.cuh); parts: PART_EZ = Euler-z pass, PART_EXY = plane pass (Euler y, x + diffusion)
+         const int mparts = (g_march & 2) ? parts : (parts & PART_EZ);
          const cudaError_t em = (scheme == HTR_SCHEME_HYBRID)
-            ? launchMarch<HTR_SCHEME_HYBRID>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, parts)
-            : launchMarch<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, parts);
-         return cuerr(em);
+            ? launchMarch<HTR_SCHEME_HYBRID>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, mparts)
+            : launchMarch<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, mparts);
+         if (em != cudaSuccess || (g_march & 2)) return cuerr(em);
+         parts &= ~PART_EZ;               // the staged kernels do the rest
       }
       cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
          ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts)

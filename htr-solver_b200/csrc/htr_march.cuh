@@ -33,8 +33,9 @@
 #pragma once
 #include "htr_fast.cuh"
 
+// resident CTAs per SM the register allocation aims at (B200, 512^3 AirMix: Euler-z march 15.4 ms at 2, 14.4 ms at 3)
 #ifndef HTR_MZ_MINB
-#define HTR_MZ_MINB 2
+#define HTR_MZ_MINB 3
 #endif
 #ifndef HTR_MP_MINB
 #define HTR_MP_MINB 2
@@ -67,34 +68,51 @@ HTR_DEV int wrap1(int c, const int lo, const int hi) {
    return c;
 }
 
-// KG flux of the face between points c2 and c3 of the six-point stencil c0..c5 (Std_node); arithmetic of
-// fast::kgStdFlux / kgFaceFlux (src/prometeo_rhs.inl:42-135)
-template<int dir>
-HTR_DEV void kgFlux6(double *Flux, const KGPoint &c0, const KGPoint &c1, const KGPoint &c2, const KGPoint &c3,
-                     const KGPoint &c4, const KGPoint &c5) {
-   const KGPoint *c[6] = {&c0, &c1, &c2, &c3, &c4, &c5};
-   double fl[nEq + 1];
-   HTR_UNROLL
-   for (int i = 0; i < nEq + 1; i++) fl[i] = 0.0;
-   HTR_UNROLL
-   for (int l = 0; l < 3; l++) {
-      double acc[nEq + 1];
+// KG flux of the face between points 2 and 3 of a six-point stencil (Std_node).  g(k, v) returns variable v of stencil
+// point k: v = 0 rho, 1 p, 2 H, 3..5 velocity, 6.. mass fractions.  Same operations per equation, in the same order, as
+// kgFaceFlux / fast::kgStdFlux (src/prometeo_rhs.inl:42-135: S = (rho_a+rho_b)*(-(un_a+un_b))*(phi_a+phi_b) summed over the
+// pairs (2,3) | (2,4) (1,3) | (2,5) (1,4) (0,3), weighted by KennedyCoeff), but with the equations in the OUTER loop: the
+// six pair coefficients are formed once and one transported variable is live at a time (a fifth of the registers).
+template<int dir, class Get>
+HTR_DEV void kgFluxStream(double *Flux, const Get &g) {
+   double rv[6];
+   {
+      double rho[6], un[6];
       HTR_UNROLL
-      for (int i = 0; i < nEq + 1; i++) acc[i] = 0.0;
-      HTR_UNROLL
-      for (int m = 0; m <= l; m++) {
-         double S[nEq + 1];
-         kgPair(S, *c[2 - m], *c[2 - m + l + 1]);
-         HTR_UNROLL
-         for (int i = 0; i < nEq + 1; i++) acc[i] += S[i];
-      }
-      const double cl = c_KennedyCoeff[Std_node][l];
-      HTR_UNROLL
-      for (int i = 0; i < nEq + 1; i++) fl[i] += cl*acc[i];
+      for (int k = 0; k < 6; k++) { rho[k] = g(k, 0); un[k] = g(k, 3 + dir); }
+      rv[0] = (rho[2] + rho[3])*(-(un[2] + un[3]));
+      rv[1] = (rho[2] + rho[4])*(-(un[2] + un[4]));
+      rv[2] = (rho[1] + rho[3])*(-(un[1] + un[3]));
+      rv[3] = (rho[2] + rho[5])*(-(un[2] + un[5]));
+      rv[4] = (rho[1] + rho[4])*(-(un[1] + un[4]));
+      rv[5] = (rho[0] + rho[3])*(-(un[0] + un[3]));
    }
+   const double k0 = c_KennedyCoeff[Std_node][0], k1 = c_KennedyCoeff[Std_node][1], k2 = c_KennedyCoeff[Std_node][2];
+   auto transported = [&](const int v) -> double {
+      double ph[6];
+      HTR_UNROLL
+      for (int k = 0; k < 6; k++) ph[k] = g(k, v);
+      double fl = 0.0;
+      { double acc = 0.0; acc += rv[0]*(ph[2] + ph[3]); fl += k0*acc; }
+      { double acc = 0.0; acc += rv[1]*(ph[2] + ph[4]); acc += rv[2]*(ph[1] + ph[3]); fl += k1*acc; }
+      { double acc = 0.0; acc += rv[3]*(ph[2] + ph[5]); acc += rv[4]*(ph[1] + ph[4]); acc += rv[5]*(ph[0] + ph[3]); fl += k2*acc; }
+      return fl;
+   };
    HTR_UNROLL
-   for (int i = 0; i < nEq; i++) Flux[i] = 0.25*fl[i];
-   Flux[irU + dir] -= fl[nEq];
+   for (int i = 0; i < nSpec; i++) Flux[i] = 0.25*transported(6 + i);
+   HTR_UNROLL
+   for (int i = 0; i < 3; i++) Flux[irU + i] = 0.25*transported(3 + i);
+   Flux[irE] = 0.25*transported(2);
+   {
+      double pr[6];
+      HTR_UNROLL
+      for (int k = 0; k < 6; k++) pr[k] = g(k, 1);
+      double fl = 0.0;
+      { double acc = 0.0; acc += (pr[2] + pr[3]); fl += k0*acc; }
+      { double acc = 0.0; acc += (pr[2] + pr[4]); acc += (pr[1] + pr[3]); fl += k1*acc; }
+      { double acc = 0.0; acc += (pr[2] + pr[5]); acc += (pr[1] + pr[4]); acc += (pr[0] + pr[3]); fl += k2*acc; }
+      Flux[irU + dir] -= fl;
+   }
 }
 
 // =============================================================================================
@@ -103,6 +121,7 @@ HTR_DEV void kgFlux6(double *Flux, const KGPoint &c0, const KGPoint &c1, const K
 constexpr int MZ_TY = 4, MZ_NT = 32*MZ_TY;
 
 struct ZRaw { double rho, p, rhoE, u[3], Y[nSpec]; };
+struct ZPt { double v[6 + nSpec]; };              // rho, p, H, u, Y: the variable order of kgFluxStream
 
 HTR_DEV void loadZRaw(ZRaw &r, const UF &f, const int n) {
    r.rho = __ldg(f.rho + n);
@@ -113,14 +132,13 @@ HTR_DEV void loadZRaw(ZRaw &r, const UF &f, const int n) {
    HTR_UNROLL
    for (int s = 0; s < nSpec; s++) r.Y[s] = __ldg(f.Y + (int64_t)n*nSpec + s);
 }
-HTR_DEV void toPoint(KGPoint &c, const ZRaw &r) {
-   c.rho = r.rho; c.p = r.p;
-   c.H = (r.rhoE + r.p)/r.rho;
+HTR_DEV void toPoint(ZPt &c, const ZRaw &r) {
+   c.v[0] = r.rho; c.v[1] = r.p;
+   c.v[2] = (r.rhoE + r.p)/r.rho;
    HTR_UNROLL
-   for (int i = 0; i < 3; i++) c.u[i] = r.u[i];
-   c.un = r.u[2];
+   for (int i = 0; i < 3; i++) c.v[3 + i] = r.u[i];
    HTR_UNROLL
-   for (int s = 0; s < nSpec; s++) c.Y[s] = r.Y[s];
+   for (int s = 0; s < nSpec; s++) c.v[6 + s] = r.Y[s];
 }
 
 template<bool HYBRID, bool CHEM>
@@ -139,75 +157,72 @@ euler_z_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ f
    const int nval = nEq*(left < 32 ? left : 32);
    #define HTR_ZOFF(z) (nxy + wrap1((z), f.blo[2], f.bhi[2])*f.SZ)       /* 32-bit cell index (host-checked range) */
 
-   // ring slot of plane q: (q - (z0-3)) mod 6; the face z+1/2 uses planes z-2 .. z+3
-   KGPoint c[6];
+   // c[k] = plane z - 2 + k of the cell being updated; rotated by register moves every step (unrolling the march six
+   // times instead removes the moves but makes the loop six times the instruction cache)
+   ZPt c[6];
    HTR_UNROLL
    for (int k = 0; k < 6; k++) { ZRaw r; loadZRaw(r, f, HTR_ZOFF(z0 - 3 + k)); toPoint(c[k], r); }
-   // rolling sensor / node-type state of the faces
-   bool s0 = true, s1 = true;                       // sensor at z-1 and z (before the step's shift: z-2, z-1)
+   auto get = [&](const int k, const int v) -> double { return c[k].v[v]; };
+   bool s0 = true, s1 = true;                       // rolling sensor values of the two planes below the face's upper cell
    if (HYBRID) { s0 = __ldg(f.sens[2] + HTR_ZOFF(z0 - 2)) != 0; s1 = __ldg(f.sens[2] + HTR_ZOFF(z0 - 1)) != 0; }
    double Fm[nEq];
    bool haveM;
-   {  // face z0 - 1/2: stencil planes z0-3 .. z0+2 = slots 0..5
+   {  // face z0 - 1/2: stencil planes z0-3 .. z0+2
       bool sm = true;
       if (HYBRID) { const bool s2 = __ldg(f.sens[2] + HTR_ZOFF(z0)) != 0; sm = s0 && s1 && s2; s0 = s1; s1 = s2; }
       haveM = sm && (__ldg(f.nT[2] + HTR_ZOFF(z0 - 1)) == Std_node);
-      kgFlux6<2>(Fm, c[0], c[1], c[2], c[3], c[4], c[5]);
+      kgFluxStream<2>(Fm, get);
    }
-   ZRaw nx;                                          // plane z+3 of the step being prepared (one step ahead)
+   ZRaw nx;                                          // plane z+3 of the next step, requested one step ahead
    loadZRaw(nx, f, HTR_ZOFF(z0 + 3));
 
-   for (int zb = z0; zb <= z1; zb += 6) {
+   #pragma unroll 1
+   for (int z = z0; z <= z1; z++) {
       HTR_UNROLL
-      for (int s = 0; s < 6; s++) {
-         const int z = zb + s;
-         if (z <= z1) {                             // block-uniform
-            toPoint(c[s], nx);                      // plane z+3 replaces plane z-3
-            if (z < z1) loadZRaw(nx, f, HTR_ZOFF(z + 4));
-            const int n = HTR_ZOFF(z);
-            double Tc = 0.0;
-            if (CHEM) Tc = __ldg(f.T + n);
-            const double mz = __ldg(f.me[2] + n);
-            bool sm = true;
-            if (HYBRID) { const bool s2 = __ldg(f.sens[2] + HTR_ZOFF(z + 1)) != 0; sm = s0 && s1 && s2; s0 = s1; s1 = s2; }
-            const bool haveP = sm && (__ldg(f.nT[2] + n) == Std_node);
-            double Fp[nEq];
-            kgFlux6<2>(Fp, c[(s + 1)%6], c[(s + 2)%6], c[(s + 3)%6], c[(s + 4)%6], c[(s + 5)%6], c[s]);
-            double base[nEq];
-            HTR_UNROLL
-            for (int e = 0; e < nEq; e++) base[e] = 0.0;
-            if (CHEM) {
-               const KGPoint &o = c[(s + 3)%6];      // own plane z
-               double w[nSpec];
-               mix::GetProductionRates(w, o.rho, o.p, Tc, o.Y);
-               HTR_UNROLL
-               for (int e = 0; e < nSpec; e++) base[e] += w[e];
-            }
-            const bool deferred = !(haveP && haveM);
-            if (!deferred) {
-               HTR_UNROLL
-               for (int e = 0; e < nEq; e++) base[e] += mz*(Fp[e] - Fm[e]);
-            }
-            HTR_UNROLL
-            for (int e = 0; e < nEq; e++) Fm[e] = Fp[e];
-            haveM = haveP;
-            if (act) {
-               mask[((int64_t)z*f.n[1] + y)*f.n[0] + x] = deferred;
-               if (deferred) *flag = 1;
-            }
-            // the row of 32 cells leaves as one contiguous span of 32*nEq doubles
-            double *so = sOut[j];
-            HTR_UNROLL
-            for (int e = 0; e < nEq; e++) so[i*nEq + e] = base[e];
-            __syncwarp();
-            if (rowOK) {
-               double *row = f.Ct + ((int64_t)x0 + (int64_t)y*f.SY + (int64_t)z*f.SZ)*nEq;
-               HTR_UNROLL
-               for (int e = 0; e < nEq; e++) { const int m = e*32 + i; if (m < nval) row[m] = so[m]; }
-            }
-            __syncwarp();
-         }
+      for (int k = 0; k < 5; k++) c[k] = c[k + 1];
+      toPoint(c[5], nx);
+      if (z < z1) loadZRaw(nx, f, HTR_ZOFF(z + 4));
+      const int n = HTR_ZOFF(z);
+      double Tc = 0.0;
+      if (CHEM) Tc = __ldg(f.T + n);
+      const double mz = __ldg(f.me[2] + n);
+      bool sm = true;
+      if (HYBRID) { const bool s2 = __ldg(f.sens[2] + HTR_ZOFF(z + 1)) != 0; sm = s0 && s1 && s2; s0 = s1; s1 = s2; }
+      const bool haveP = sm && (__ldg(f.nT[2] + n) == Std_node);
+      double Fp[nEq];
+      kgFluxStream<2>(Fp, get);
+      double base[nEq];
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) base[e] = 0.0;
+      if (CHEM) {
+         double w[nSpec];
+         mix::GetProductionRates(w, c[2].v[0], c[2].v[1], Tc, &c[2].v[6]);
+         HTR_UNROLL
+         for (int e = 0; e < nSpec; e++) base[e] += w[e];
       }
+      const bool deferred = !(haveP && haveM);
+      if (!deferred) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) base[e] += mz*(Fp[e] - Fm[e]);
+      }
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) Fm[e] = Fp[e];
+      haveM = haveP;
+      if (act) {
+         mask[((int64_t)z*f.n[1] + y)*f.n[0] + x] = deferred;
+         if (deferred) *flag = 1;
+      }
+      // the row of 32 cells leaves as one contiguous span of 32*nEq doubles
+      double *so = sOut[j];
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) so[i*nEq + e] = base[e];
+      __syncwarp();
+      if (rowOK) {
+         double *row = f.Ct + ((int64_t)x0 + (int64_t)y*f.SY + (int64_t)z*f.SZ)*nEq;
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) { const int m = e*32 + i; if (m < nval) row[m] = so[m]; }
+      }
+      __syncwarp();
    }
    #undef HTR_ZOFF
 }
@@ -219,57 +234,34 @@ constexpr int PW = 37, PR = 13, NCE = PW*PR;          // stencil box: columns -2
 constexpr int DW = 33, DR = 9, NCD = DW*DR;           // diffusion box: columns 0..32, rows 0..8
 constexpr int PNT = 256;
 constexpr int NG = 7;                                  // staged derivatives: dUdX dVdX dUdY dVdY dUdZ dVdZ dWdZ
-// shared-memory map (doubles)
+// shared-memory map (doubles).  R1 is time-shared: the E data of a plane is dead when its D data is staged.
 constexpr int OFF_V = 0;                               // [3][NCE*3] velocity ring, AoS
 constexpr int OFF_R1 = 3*NCE*3;
 constexpr int E_RHO = 0, E_P = NCE, E_H = 2*NCE, E_Y = 3*NCE, E_END = NCE*(3 + nSpec);
-constexpr int OFF_SF = E_END;                          // [nEq][PNT] face exchange (beyond the E data, inside the D data)
-constexpr int OFF_SO = OFF_SF + nEq*PNT;               // [8][32*nEq] output rows
 constexpr int D_RHO = 0, D_MU = NCD, D_LAM = 2*NCD, D_T = 3*NCD, D_X = 4*NCD, D_DI = D_X + NCD*nSpec,
               D_RY = D_DI + NCD*nSpec, D_G = D_RY + NCD*nSpec, D_END = D_G + NG*NCD;
-constexpr int R1_DBL = (OFF_SO + 8*32*nEq > D_END) ? OFF_SO + 8*32*nEq : D_END;
-constexpr int NBYTES = 2*NCE + 2*PNT;                  // sensX, sensY on the stencil box; have-flags; deferred flags
-constexpr size_t PM_SMEM = sizeof(double)*(OFF_R1 + R1_DBL) + ((NBYTES + 15)/16)*16;
+constexpr int OFF_SO = E_END;                          // [8][32*nEq] output rows: beyond the E data, inside the (dead) D data
+constexpr int OFF_SB = OFF_SO + 8*32*nEq;              // sensor bytes of the stencil box (E phase only), inside the D data
+constexpr int OFF_SF = D_END;                          // [nEq][PNT] y-face exchange, aliases nothing
+constexpr int R1_DBL = OFF_SF + nEq*PNT;
+static_assert(OFF_SB + 2*512/8 <= D_END, "sensor bytes must fit inside the time-shared region");
+constexpr size_t PM_SMEM = sizeof(double)*(OFF_R1 + R1_DBL) + 2*PNT;
 
-// operands of one cell of a diffusion face
-struct DOps { double rho, mu, lam, T, u[3], X[nSpec], Di[nSpec], rY[nSpec], g[4]; };
-
-// own cell of plane n (element offset) straight from global memory; u and g are filled by the caller
-HTR_DEV void loadDOps(DOps &o, const UF &f, const int n) {
-   o.rho = __ldg(f.rho + n); o.mu = __ldg(f.mu + n); o.lam = __ldg(f.lam + n); o.T = __ldg(f.T + n);
+// Diffusion flux of the face between cells P and Q = P + 1 along dir (Std_node).  P(v), Q(v) return operand v of the
+// cell: 0 rho, 1 mu, 2 lam, 3 T, 4..6 velocity, 7.. X_i, then D_i, then rho Y_i, then the four transverse derivatives
+//   dir 0: dVdY dUdY dUdZ dWdZ    dir 1: dUdX dVdX dVdZ dWdZ    dir 2: dUdX dWdX dVdY dWdY
+// Expression for expression fast::diffFaceStd / diffusionFaceFlux (src/prometeo_rhs.inl:1058-1215).
+constexpr int DV_X = 7, DV_DI = 7 + nSpec, DV_RY = 7 + 2*nSpec, DV_G = 7 + 3*nSpec, DV_N = DV_G + 4;
+template<int dir, class GP, class GQ>
+HTR_DEV void diffFaceStream(double *Flux, const GP &P, const GQ &Q, const double m_s) {
+   const double rho_s = interpStd(P(0), Q(0));
+   double XP[nSpec], XQ[nSpec];
    HTR_UNROLL
-   for (int s = 0; s < nSpec; s++) {
-      o.X[s] = __ldg(f.X + (int64_t)n*nSpec + s);
-      o.Di[s] = __ldg(f.Di + (int64_t)n*nSpec + s);
-      o.rY[s] = __ldg(f.C + (int64_t)n*nEq + s);
-   }
-}
-// staged cell `idx` of the diffusion box; gA..gD = slots of the staged derivatives the face of this direction uses
-HTR_DEV void ldsDOps(DOps &o, const double *__restrict__ d, const double *__restrict__ v, const int idx, const int vidx,
-                     const int gA, const int gB, const int gC, const int gD) {
-   o.rho = d[D_RHO + idx]; o.mu = d[D_MU + idx]; o.lam = d[D_LAM + idx]; o.T = d[D_T + idx];
-   HTR_UNROLL
-   for (int c = 0; c < 3; c++) o.u[c] = v[vidx*3 + c];
-   HTR_UNROLL
-   for (int s = 0; s < nSpec; s++) {
-      o.X[s] = d[D_X + idx*nSpec + s];
-      o.Di[s] = d[D_DI + idx*nSpec + s];
-      o.rY[s] = d[D_RY + idx*nSpec + s];
-   }
-   o.g[0] = d[D_G + gA*NCD + idx]; o.g[1] = d[D_G + gB*NCD + idx];
-   o.g[2] = d[D_G + gC*NCD + idx]; o.g[3] = d[D_G + gD*NCD + idx];
-}
-
-// Diffusion flux of the face between cells P and Q = P + 1 along dir (Std_node).  Expression for expression
-// fast::diffFaceStd / diffusionFaceFlux (src/prometeo_rhs.inl:1058-1215); g[] holds the transverse derivatives in
-// the order   dir 0: dVdY dUdY dUdZ dWdZ    dir 1: dUdX dVdX dVdZ dWdZ    dir 2: dUdX dWdX dVdY dWdY
-template<int dir>
-HTR_DEV void diffFace(double *Flux, const DOps &P, const DOps &Q, const double m_s) {
-   const double rho_s = interpStd(P.rho, Q.rho);
-   const double iMixW_s = 1.0/interpStd(mix::GetMolarWeightFromXi(P.X), mix::GetMolarWeightFromXi(Q.X));
-   const double Tp = P.T, Tq = Q.T;
+   for (int i = 0; i < nSpec; i++) { XP[i] = P(DV_X + i); XQ[i] = Q(DV_X + i); }
+   const double iMixW_s = 1.0/interpStd(mix::GetMolarWeightFromXi(XP), mix::GetMolarWeightFromXi(XQ));
+   const double Tp = P(3), Tq = Q(3);
    const double T_s = interpStd(Tp, Tq);
-   double heatFlux = interpStd(P.lam, Q.lam)*m_s*(Tp - Tq);
+   double heatFlux = interpStd(P(2), Q(2))*m_s*(Tp - Tq);
 
    double hi[nSpec];
    mix::GetSpeciesEnthalpies(hi, T_s);
@@ -277,26 +269,26 @@ HTR_DEV void diffFace(double *Flux, const DOps &P, const DOps &Q, const double m
    double ViCorr = 0.0;
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
-      const double YiVi = interpStd(P.Di[i], Q.Di[i])*m_s*(P.X[i] - Q.X[i])*mix::GetSpeciesMolarWeight(i)*iMixW_s;
+      const double YiVi = interpStd(P(DV_DI + i), Q(DV_DI + i))*m_s*(XP[i] - XQ[i])*mix::GetSpeciesMolarWeight(i)*iMixW_s;
       Flux[i] = -rho_s*YiVi;
       heatFlux += rho_s*YiVi*hi[i];
       ViCorr += YiVi;
    }
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
-      const double rhoYiViCorr = interpStd(P.rY[i], Q.rY[i])*ViCorr;
+      const double rhoYiViCorr = interpStd(P(DV_RY + i), Q(DV_RY + i))*ViCorr;
       Flux[i] += rhoYiViCorr;
       heatFlux -= rhoYiViCorr*hi[i];
    }
 
-   double dN[3];
+   double up[3], uq[3], dN[3];
    HTR_UNROLL
-   for (int i = 0; i < 3; i++) dN[i] = m_s*(Q.u[i] - P.u[i]);
-   const double mu_s = interpStd(P.mu, Q.mu);
-   const double A = interpStd(P.g[0], Q.g[0]);
-   const double Bv = interpStd(P.g[1], Q.g[1]);
-   const double Cv = interpStd(P.g[2], Q.g[2]);
-   const double Dv = interpStd(P.g[3], Q.g[3]);
+   for (int i = 0; i < 3; i++) { up[i] = P(4 + i); uq[i] = Q(4 + i); dN[i] = m_s*(uq[i] - up[i]); }
+   const double mu_s = interpStd(P(1), Q(1));
+   const double A = interpStd(P(DV_G + 0), Q(DV_G + 0));
+   const double Bv = interpStd(P(DV_G + 1), Q(DV_G + 1));
+   const double Cv = interpStd(P(DV_G + 2), Q(DV_G + 2));
+   const double Dv = interpStd(P(DV_G + 3), Q(DV_G + 3));
    double sigma[3];
    if (dir == 0) {
       sigma[0] = mu_s*(4*dN[0] - 2*A - 2*Dv)/3;
@@ -315,11 +307,23 @@ HTR_DEV void diffFace(double *Flux, const DOps &P, const DOps &Q, const double m
    for (int i = 0; i < 3; i++) Flux[irU + i] = sigma[i];
    double uSigma = 0.0;
    HTR_UNROLL
-   for (int i = 0; i < 3; i++) uSigma += interpStd(P.u[i], Q.u[i])*sigma[i];
+   for (int i = 0; i < 3; i++) uSigma += interpStd(up[i], uq[i])*sigma[i];
    Flux[irE] = (uSigma - heatFlux);
 }
 
-// x/y derivatives of the velocity at stencil-box cell v of one staged velocity plane, as the z face uses them:
+// operands of the own cell of one plane in registers (the z face's upper cell; both cells in the prologue)
+struct DOps { double v[DV_N]; };
+HTR_DEV void loadDOps(DOps &o, const UF &f, const int n) {
+   o.v[0] = __ldg(f.rho + n); o.v[1] = __ldg(f.mu + n); o.v[2] = __ldg(f.lam + n); o.v[3] = __ldg(f.T + n);
+   HTR_UNROLL
+   for (int s = 0; s < nSpec; s++) {
+      o.v[DV_X + s] = __ldg(f.X + (int64_t)n*nSpec + s);
+      o.v[DV_DI + s] = __ldg(f.Di + (int64_t)n*nSpec + s);
+      o.v[DV_RY + s] = __ldg(f.C + (int64_t)n*nEq + s);
+   }
+}
+
+// x/y derivatives of the velocity at stencil-box cell vi of one staged velocity plane, as the z face uses them:
 // g = dUdX dWdX dVdY dWdY
 HTR_DEV void zFaceDerivs(double *g, const double *__restrict__ v, const int vi, const double mx, const double my) {
    g[0] = derivStd(v[(vi - 1)*3 + 0], v[vi*3 + 0], v[(vi + 1)*3 + 0], mx);
@@ -335,9 +339,9 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
    double *sV = smem + OFF_V;
    double *R1 = smem + OFF_R1;
    double *sF = R1 + OFF_SF;
-   uint8_t *sSx = reinterpret_cast<uint8_t*>(R1 + R1_DBL);
-   uint8_t *sSy = sSx + NCE;
-   uint8_t *sHave = sSy + NCE;
+   uint8_t *sSx = reinterpret_cast<uint8_t*>(R1 + OFF_SB);
+   uint8_t *sSy = sSx + 512;
+   uint8_t *sHave = reinterpret_cast<uint8_t*>(R1 + R1_DBL);
    uint8_t *sDef = sHave + PNT;
 
    const int i = threadIdx.x, j = threadIdx.y, tid = j*32 + i;
@@ -367,19 +371,17 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
    // diffusion box: cell tid in full (A); one of six parts of cell 256 + tid/6 (B)
    int dIdx[2], dOfs[2], dVi[2]; bool dV[2];
    int partB = -1;
-   if (DIFF) {
-      HTR_UNROLL
-      for (int k = 0; k < 2; k++) {
-         const int bd = (k == 0) ? tid : PNT + tid/6;
-         const int row = bd/DW, col = bd - row*DW;
-         const int gx = cx0 + col, gy = cy0 + row;
-         dV[k] = bd < NCD && gx <= f.n[0] && gy <= f.n[1] && (k == 0 || tid < 6*(NCD - PNT));
-         dIdx[k] = bd < NCD ? bd : 0;
-         dVi[k] = (row + 2)*PW + col + 2;
-         dOfs[k] = dV[k] ? wrap1(gx, f.blo[0], f.bhi[0]) + wrap1(gy, f.blo[1], f.bhi[1])*f.SY : 0;
-      }
-      partB = dV[1] ? tid%6 : -1;
+   HTR_UNROLL
+   for (int k = 0; k < 2; k++) {
+      const int bd = (k == 0) ? tid : PNT + tid/6;
+      const int row = bd/DW, col = bd - row*DW;
+      const int gx = cx0 + col, gy = cy0 + row;
+      dV[k] = bd < NCD && gx <= f.n[0] && gy <= f.n[1] && (k == 0 || tid < 6*(NCD - PNT));
+      dIdx[k] = bd < NCD ? bd : 0;
+      dVi[k] = (row + 2)*PW + col + 2;
+      dOfs[k] = dV[k] ? wrap1(gx, f.blo[0], f.bhi[0]) + wrap1(gy, f.blo[1], f.bhi[1])*f.SY : 0;
    }
+   partB = dV[1] ? tid%6 : -1;
    #define HTR_ZP(z) (wrap1((z), f.blo[2], f.bhi[2])*f.SZ)                /* 32-bit cell index of the plane (host-checked range) */
 
    // velocity plane z -> ring slot
@@ -393,55 +395,57 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
             for (int c = 0; c < 3; c++) v[be*3 + c] = __ldg(f.vel + n + c);
          }
    };
-   // any node type of plane z on the diffusion box that the fast arithmetic does not cover?
-   auto badNodes = [&](const int zo) -> bool {
+
+   // ---- prologue ------------------------------------------------------------------------------------------
+   // node types of the whole chunk (planes z0-1 .. z1+1 of the diffusion box): all loads are independent, one
+   // barrier.  A chunk with any node the Std_node arithmetic does not cover is left to the generic kernels.
+   {
       bool bad = false;
-      if (DIFF) {
+      for (int z = z0 - 1; z <= z1 + 1; z++) {
+         const int zo = HTR_ZP(z);
          if (dV[0]) {
             const int n = dOfs[0] + zo;
-            bad = (__ldg(f.nT[0] + n) != Std_node) || (__ldg(f.nT[1] + n) != Std_node) || (__ldg(f.nT[2] + n) != Std_node);
+            bad = bad || (__ldg(f.nT[0] + n) != Std_node) || (__ldg(f.nT[1] + n) != Std_node) || (__ldg(f.nT[2] + n) != Std_node);
          }
          if (partB == 0) {
             const int n = dOfs[1] + zo;
             bad = bad || (__ldg(f.nT[0] + n) != Std_node) || (__ldg(f.nT[1] + n) != Std_node) || (__ldg(f.nT[2] + n) != Std_node);
          }
-      } else if (faceAct) {
-         const int n = nOwn + zo;
-         bad = (__ldg(f.nT[0] + n) != Std_node) || (__ldg(f.nT[1] + n) != Std_node);
       }
-      return bad;
-   };
-
-   // ---- prologue: velocity planes z0-1, z0; node types of z0-1, z0; diffusion z face z0-1/2 ------------
-   // ring slot of plane z: (z - z0 + 1) mod 3
-   bool badP = false, badC = false;
+      if (DIFF) { stageV(sV, HTR_ZP(z0 - 1)); stageV(sV + NCE*3, HTR_ZP(z0)); }
+      if (__syncthreads_or(bad)) {
+         if (upd) {
+            for (int p = z0; p <= z1; p++) mask[((int64_t)p*f.n[1] + y)*f.n[0] + x] = 1;
+            *flag = 1;
+         }
+         return;
+      }
+   }
+   // velocity planes z0-1, z0 are staged (ring slot of plane z: (z - z0 + 1) mod 3); diffusion z face z0-1/2
    double FzM[nEq], gC[4];                               // diffusion z flux of face p-1/2; z-face derivatives of plane p
    if (DIFF) {
-      stageV(sV, HTR_ZP(z0 - 1));
-      stageV(sV + NCE*3, HTR_ZP(z0));
-      badP = __syncthreads_or(badNodes(HTR_ZP(z0 - 1)));
-      badC = __syncthreads_or(badNodes(HTR_ZP(z0)));
       DOps P, Q;
       const int nm = nOwn + HTR_ZP(z0 - 1), nc = nOwn + HTR_ZP(z0);
       loadDOps(P, f, nm); loadDOps(Q, f, nc);
       HTR_UNROLL
-      for (int c = 0; c < 3; c++) { P.u[c] = sV[ownE*3 + c]; Q.u[c] = sV[NCE*3 + ownE*3 + c]; }
-      zFaceDerivs(P.g, sV, ownE, __ldg(f.md[0] + nm), __ldg(f.md[1] + nm));
+      for (int c = 0; c < 3; c++) { P.v[4 + c] = sV[ownE*3 + c]; Q.v[4 + c] = sV[NCE*3 + ownE*3 + c]; }
+      zFaceDerivs(&P.v[DV_G], sV, ownE, __ldg(f.md[0] + nm), __ldg(f.md[1] + nm));
       zFaceDerivs(gC, sV + NCE*3, ownE, __ldg(f.md[0] + nc), __ldg(f.md[1] + nc));
       HTR_UNROLL
-      for (int k = 0; k < 4; k++) Q.g[k] = gC[k];
-      diffFace<2>(FzM, P, Q, __ldg(f.ms[2] + nm));
+      for (int k = 0; k < 4; k++) Q.v[DV_G + k] = gC[k];
+      diffFaceStream<2>(FzM, [&](const int v) { return P.v[v]; }, [&](const int v) { return Q.v[v]; }, __ldg(f.ms[2] + nm));
    }
 
+   #pragma unroll 1
    for (int p = z0; p <= z1; p++) {
       const int k3 = (p - z0)%3;
-      double *vm = sV + k3*(NCE*3);                                 // plane p-1
-      double *vc = sV + ((k3 + 1)%3)*(NCE*3);                       // plane p
+      const double *vm = sV + k3*(NCE*3);                           // plane p-1
+      const double *vc = sV + ((k3 + 1)%3)*(NCE*3);                 // plane p
       double *vn = sV + ((k3 + 2)%3)*(NCE*3);                       // plane p+1
       const int zo = HTR_ZP(p), zn = HTR_ZP(p + 1);
       const int nO = nOwn + zo;
 
-      // ---- (1) stage the E data of plane p, the velocity of plane p+1 (DIFF) or p, the sensors ----------
+      // ---- (1) stage the E data of plane p, the sensors, the velocity of plane p+1 (DIFF) or p --------------
       HTR_UNROLL
       for (int k = 0; k < 2; k++) {
          const int be = tid + PNT*k;
@@ -456,45 +460,32 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
             if (HYBRID) { sSx[be] = __ldg(f.sens[0] + n); sSy[be] = __ldg(f.sens[1] + n); }
          }
       }
-      if (DIFF) stageV(vn, zn); else stageV(vc, zo);
-      // barrier B1, which also gathers the node-type check of plane p+1 (DIFF) or p
-      const bool badN = __syncthreads_or(badNodes(DIFF ? zn : zo)) != 0;
-      if (!DIFF) badC = false;
-      const bool bad3 = badP || badC || badN;                                      // CTA-uniform: this plane's cells are deferred
-      const bool badF = badC || badN;                                              // the faces of this step are not computed
+      if (DIFF) stageV(vn, zn); else stageV(sV + ((k3 + 1)%3)*(NCE*3), zo);
+      __syncthreads();                                                             // B1
 
-      // ---- (2) Euler y and x faces ----------------------------------------------------------------------
-      double Fy[nEq], Fx[nEq];
+      // ---- (2) Euler y face (published through sF), Euler x face (registers) ------------------------------------
       bool haveY = false, haveX = false;
-      if (faceAct && !badF) {
+      if (faceAct) {
          haveY = !HYBRID || (sSy[ownE - PW] && sSy[ownE] && sSy[ownE + PW]);
          haveX = !HYBRID || (sSx[ownE - 1] && sSx[ownE] && sSx[ownE + 1]);
-         auto pt = [&](KGPoint &c, const int idx, const int dir) {
-            c.rho = R1[E_RHO + idx]; c.p = R1[E_P + idx]; c.H = R1[E_H + idx];
-            HTR_UNROLL
-            for (int q = 0; q < 3; q++) c.u[q] = vc[idx*3 + q];
-            HTR_UNROLL
-            for (int s = 0; s < nSpec; s++) c.Y[s] = R1[E_Y + idx*nSpec + s];
-            c.un = c.u[dir];
-         };
-         if (haveY) {
-            KGPoint c[6];
-            HTR_UNROLL
-            for (int k = 0; k < 6; k++) pt(c[k], ownE + (k - 2)*PW, 1);
-            kgFlux6<1>(Fy, c[0], c[1], c[2], c[3], c[4], c[5]);
-         }
-         if (haveX) {
-            KGPoint c[6];
-            HTR_UNROLL
-            for (int k = 0; k < 6; k++) pt(c[k], ownE + (k - 2), 0);
-            kgFlux6<0>(Fx, c[0], c[1], c[2], c[3], c[4], c[5]);
-         }
       }
-      if (!haveY) { HTR_UNROLL for (int e = 0; e < nEq; e++) Fy[e] = 0.0; }
-      if (!haveX) { HTR_UNROLL for (int e = 0; e < nEq; e++) Fx[e] = 0.0; }
-      HTR_UNROLL
-      for (int e = 0; e < nEq; e++) sF[e*PNT + tid] = Fy[e];
-      sHave[tid] = haveY;
+      {
+         double Fy[nEq];
+         if (haveY)
+            kgFluxStream<1>(Fy, [&](const int k, const int v) -> double {
+               const int idx = ownE + (k - 2)*PW;
+               return v < 3 ? R1[v*NCE + idx] : (v < 6 ? vc[idx*3 + (v - 3)] : R1[E_Y + idx*nSpec + (v - 6)]); });
+         else { HTR_UNROLL for (int e = 0; e < nEq; e++) Fy[e] = 0.0; }
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) sF[e*PNT + tid] = Fy[e];
+         sHave[tid] = haveY;
+      }
+      double Fx[nEq];
+      if (haveX)
+         kgFluxStream<0>(Fx, [&](const int k, const int v) -> double {
+            const int idx = ownE + (k - 2);
+            return v < 3 ? R1[v*NCE + idx] : (v < 6 ? vc[idx*3 + (v - 3)] : R1[E_Y + idx*nSpec + (v - 6)]); });
+      else { HTR_UNROLL for (int e = 0; e < nEq; e++) Fx[e] = 0.0; }
       double ct[nEq];
       if (upd) {
          HTR_UNROLL
@@ -503,143 +494,138 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
       __syncthreads();                                                             // B2
       bool okE = false;
       {
-         double FxM[nEq];
-         HTR_UNROLL
-         for (int e = 0; e < nEq; e++) FxM[e] = __shfl_up_sync(0xffffffffu, Fx[e], 1);
          const bool haveXm = __shfl_up_sync(0xffffffffu, (int)haveX, 1) != 0;
-         if (upd) {
-            okE = haveX && haveXm && haveY && sHave[tid - 32];
-            const double my = __ldg(f.me[1] + nO), mx = __ldg(f.me[0] + nO);
-            HTR_UNROLL
-            for (int e = 0; e < nEq; e++) {
+         const double my = upd ? __ldg(f.me[1] + nO) : 0.0, mx = upd ? __ldg(f.me[0] + nO) : 0.0;
+         if (upd) okE = haveX && haveXm && haveY && sHave[tid - 32];
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) {
+            const double FxM = __shfl_up_sync(0xffffffffu, Fx[e], 1);
+            if (upd) {
                double v = ct[e];
-               v += my*(Fy[e] - sF[e*PNT + tid - 32]);
-               v += mx*(Fx[e] - FxM[e]);
+               v += my*(sF[e*PNT + tid] - sF[e*PNT + tid - 32]);
+               v += mx*(Fx[e] - FxM);
                ct[e] = v;
             }
          }
       }
 
       if (DIFF) {
-         // upper operands of the z face p+1/2 (own cell of plane p+1): in flight during the staging below
          const int nN = nOwn + zn;
-         __syncthreads();                                                          // B3: sF has been read
-         // ---- (3) stage the diffusion operands of plane p and the velocity derivatives --------------------
-         if (!badF) {
-            if (dV[0]) {
-               const int idx = dIdx[0], vi = dVi[0];
-               const int n = dOfs[0] + zo;
+         // ---- (3) stage the diffusion operands of plane p and the velocity derivatives (the E data is dead) ----
+         if (dV[0]) {
+            const int idx = dIdx[0], vi = dVi[0];
+            const int n = dOfs[0] + zo;
+            R1[D_RHO + idx] = __ldg(f.rho + n); R1[D_MU + idx] = __ldg(f.mu + n);
+            R1[D_LAM + idx] = __ldg(f.lam + n); R1[D_T + idx] = __ldg(f.T + n);
+            HTR_UNROLL
+            for (int s = 0; s < nSpec; s++) {
+               R1[D_X + idx*nSpec + s] = __ldg(f.X + (int64_t)n*nSpec + s);
+               R1[D_DI + idx*nSpec + s] = __ldg(f.Di + (int64_t)n*nSpec + s);
+               R1[D_RY + idx*nSpec + s] = __ldg(f.C + (int64_t)n*nEq + s);
+            }
+            const double mx = __ldg(f.md[0] + n), my = __ldg(f.md[1] + n), mz = __ldg(f.md[2] + n);
+            R1[D_G + 0*NCD + idx] = derivStd(vc[(vi - 1)*3 + 0], vc[vi*3 + 0], vc[(vi + 1)*3 + 0], mx);
+            R1[D_G + 1*NCD + idx] = derivStd(vc[(vi - 1)*3 + 1], vc[vi*3 + 1], vc[(vi + 1)*3 + 1], mx);
+            R1[D_G + 2*NCD + idx] = derivStd(vc[(vi - PW)*3 + 0], vc[vi*3 + 0], vc[(vi + PW)*3 + 0], my);
+            R1[D_G + 3*NCD + idx] = derivStd(vc[(vi - PW)*3 + 1], vc[vi*3 + 1], vc[(vi + PW)*3 + 1], my);
+            HTR_UNROLL
+            for (int c = 0; c < 3; c++)
+               R1[D_G + (4 + c)*NCD + idx] = derivStd(vm[vi*3 + c], vc[vi*3 + c], vn[vi*3 + c], mz);
+         }
+         if (partB >= 0) {
+            const int idx = dIdx[1], vi = dVi[1];
+            const int n = dOfs[1] + zo;
+            if (partB == 0) {
                R1[D_RHO + idx] = __ldg(f.rho + n); R1[D_MU + idx] = __ldg(f.mu + n);
                R1[D_LAM + idx] = __ldg(f.lam + n); R1[D_T + idx] = __ldg(f.T + n);
+            } else if (partB == 1) {
                HTR_UNROLL
-               for (int s = 0; s < nSpec; s++) {
-                  R1[D_X + idx*nSpec + s] = __ldg(f.X + (int64_t)n*nSpec + s);
-                  R1[D_DI + idx*nSpec + s] = __ldg(f.Di + (int64_t)n*nSpec + s);
-                  R1[D_RY + idx*nSpec + s] = __ldg(f.C + (int64_t)n*nEq + s);
-               }
-               const double mx = __ldg(f.md[0] + n), my = __ldg(f.md[1] + n), mz = __ldg(f.md[2] + n);
+               for (int s = 0; s < nSpec; s++) R1[D_X + idx*nSpec + s] = __ldg(f.X + (int64_t)n*nSpec + s);
+            } else if (partB == 2) {
+               HTR_UNROLL
+               for (int s = 0; s < nSpec; s++) R1[D_DI + idx*nSpec + s] = __ldg(f.Di + (int64_t)n*nSpec + s);
+            } else if (partB == 3) {
+               HTR_UNROLL
+               for (int s = 0; s < nSpec; s++) R1[D_RY + idx*nSpec + s] = __ldg(f.C + (int64_t)n*nEq + s);
+            } else if (partB == 4) {
+               const double mx = __ldg(f.md[0] + n), my = __ldg(f.md[1] + n);
                R1[D_G + 0*NCD + idx] = derivStd(vc[(vi - 1)*3 + 0], vc[vi*3 + 0], vc[(vi + 1)*3 + 0], mx);
                R1[D_G + 1*NCD + idx] = derivStd(vc[(vi - 1)*3 + 1], vc[vi*3 + 1], vc[(vi + 1)*3 + 1], mx);
                R1[D_G + 2*NCD + idx] = derivStd(vc[(vi - PW)*3 + 0], vc[vi*3 + 0], vc[(vi + PW)*3 + 0], my);
                R1[D_G + 3*NCD + idx] = derivStd(vc[(vi - PW)*3 + 1], vc[vi*3 + 1], vc[(vi + PW)*3 + 1], my);
+            } else {
+               const double mz = __ldg(f.md[2] + n);
                HTR_UNROLL
                for (int c = 0; c < 3; c++)
                   R1[D_G + (4 + c)*NCD + idx] = derivStd(vm[vi*3 + c], vc[vi*3 + c], vn[vi*3 + c], mz);
             }
-            if (partB >= 0) {
-               const int idx = dIdx[1], vi = dVi[1];
-               const int n = dOfs[1] + zo;
-               if (partB == 0) {
-                  R1[D_RHO + idx] = __ldg(f.rho + n); R1[D_MU + idx] = __ldg(f.mu + n);
-                  R1[D_LAM + idx] = __ldg(f.lam + n); R1[D_T + idx] = __ldg(f.T + n);
-               } else if (partB == 1) {
-                  HTR_UNROLL
-                  for (int s = 0; s < nSpec; s++) R1[D_X + idx*nSpec + s] = __ldg(f.X + (int64_t)n*nSpec + s);
-               } else if (partB == 2) {
-                  HTR_UNROLL
-                  for (int s = 0; s < nSpec; s++) R1[D_DI + idx*nSpec + s] = __ldg(f.Di + (int64_t)n*nSpec + s);
-               } else if (partB == 3) {
-                  HTR_UNROLL
-                  for (int s = 0; s < nSpec; s++) R1[D_RY + idx*nSpec + s] = __ldg(f.C + (int64_t)n*nEq + s);
-               } else if (partB == 4) {
-                  const double mx = __ldg(f.md[0] + n), my = __ldg(f.md[1] + n);
-                  R1[D_G + 0*NCD + idx] = derivStd(vc[(vi - 1)*3 + 0], vc[vi*3 + 0], vc[(vi + 1)*3 + 0], mx);
-                  R1[D_G + 1*NCD + idx] = derivStd(vc[(vi - 1)*3 + 1], vc[vi*3 + 1], vc[(vi + 1)*3 + 1], mx);
-                  R1[D_G + 2*NCD + idx] = derivStd(vc[(vi - PW)*3 + 0], vc[vi*3 + 0], vc[(vi + PW)*3 + 0], my);
-                  R1[D_G + 3*NCD + idx] = derivStd(vc[(vi - PW)*3 + 1], vc[vi*3 + 1], vc[(vi + PW)*3 + 1], my);
-               } else {
-                  const double mz = __ldg(f.md[2] + n);
-                  HTR_UNROLL
-                  for (int c = 0; c < 3; c++)
-                     R1[D_G + (4 + c)*NCD + idx] = derivStd(vm[vi*3 + c], vc[vi*3 + c], vn[vi*3 + c], mz);
-               }
-            }
          }
-         __syncthreads();                                                          // B4
-         // ---- (4) diffusion faces: z (p+1/2), y, x ---------------------------------------------------------
-         double Dz[nEq], Dy[nEq], Dx[nEq];
+         // upper operands of the z face p+1/2 (own cell of plane p+1): requested before the barrier
+         DOps Qz;
          double gN[4];
-         HTR_UNROLL
-         for (int e = 0; e < nEq; e++) { Dz[e] = 0.0; Dy[e] = 0.0; Dx[e] = 0.0; }
-         if (faceAct && !badF) {       // the z face p+1/2 is the next step's minus face: it only depends on planes p, p+1
-            {
-               DOps P, Qz;
-               loadDOps(Qz, f, nN);          // upper operands of the z face p+1/2: own cell of plane p+1, straight from global
-               ldsDOps(P, R1, vc, ownD, ownE, 0, 0, 0, 0);
-               HTR_UNROLL
-               for (int k = 0; k < 4; k++) P.g[k] = gC[k];
-               HTR_UNROLL
-               for (int c = 0; c < 3; c++) Qz.u[c] = vn[ownE*3 + c];
-               zFaceDerivs(gN, vn, ownE, __ldg(f.md[0] + nN), __ldg(f.md[1] + nN));
-               HTR_UNROLL
-               for (int k = 0; k < 4; k++) Qz.g[k] = gN[k];
-               diffFace<2>(Dz, P, Qz, __ldg(f.ms[2] + nO));
-            }
-            {
-               DOps P, Q;
-               ldsDOps(P, R1, vc, ownD, ownE, 0, 1, 5, 6);
-               ldsDOps(Q, R1, vc, ownD + DW, ownE + PW, 0, 1, 5, 6);
-               diffFace<1>(Dy, P, Q, __ldg(f.ms[1] + nO));
-            }
-            {
-               DOps P, Q;
-               ldsDOps(P, R1, vc, ownD, ownE, 3, 2, 4, 6);
-               ldsDOps(Q, R1, vc, ownD + 1, ownE + 1, 3, 2, 4, 6);
-               diffFace<0>(Dx, P, Q, __ldg(f.ms[0] + nO));
-            }
+         if (faceAct) {
+            loadDOps(Qz, f, nN);
+            HTR_UNROLL
+            for (int c = 0; c < 3; c++) Qz.v[4 + c] = vn[ownE*3 + c];
+            zFaceDerivs(gN, vn, ownE, __ldg(f.md[0] + nN), __ldg(f.md[1] + nN));
+            HTR_UNROLL
+            for (int k = 0; k < 4; k++) Qz.v[DV_G + k] = gN[k];
          } else {
             HTR_UNROLL
             for (int k = 0; k < 4; k++) gN[k] = 0.0;
-            if (faceAct) zFaceDerivs(gN, vn, ownE, __ldg(f.md[0] + nN), __ldg(f.md[1] + nN));      // keeps the carried derivatives valid across a deferred plane
          }
-         __syncthreads();                                                          // B5: the D data has been read
-         HTR_UNROLL
-         for (int e = 0; e < nEq; e++) sF[e*PNT + tid] = Dy[e];
-         __syncthreads();                                                          // B6
-         {
-            double DxM[nEq];
-            HTR_UNROLL
-            for (int e = 0; e < nEq; e++) DxM[e] = __shfl_up_sync(0xffffffffu, Dx[e], 1);
+         __syncthreads();                                                          // B4
+         // ---- (4) diffusion faces.  z (p+1/2) is applied at once and becomes the next step's minus face; y is
+         //          published through sF; x stays in registers until the barrier ----------------------------------
+         // staged operand v of diffusion-box cell idx (velocity from the ring); the derivative slots depend on the face
+         #define HTR_DGET(idx, vidx, gA, gB, gC_, gD) [&](const int v) -> double { \
+            return v < 4 ? R1[v*NCD + (idx)] : (v < 7 ? vc[(vidx)*3 + (v - 4)] : (v < DV_G ? R1[D_X + (v - 7)/nSpec*(NCD*nSpec) + (idx)*nSpec + (v - 7)%nSpec] \
+                   : R1[D_G + (v == DV_G ? (gA) : (v == DV_G + 1 ? (gB) : (v == DV_G + 2 ? (gC_) : (gD))))*NCD + (idx)])); }
+         if (faceAct) {
+            double Dz[nEq];
+            diffFaceStream<2>(Dz, [&](const int v) -> double {
+                                  return v < 4 ? R1[v*NCD + ownD] : (v < 7 ? vc[ownE*3 + (v - 4)]
+                                       : (v < DV_G ? R1[D_X + (v - 7)/nSpec*(NCD*nSpec) + ownD*nSpec + (v - 7)%nSpec] : gC[v - DV_G])); },
+                               [&](const int v) -> double { return Qz.v[v]; }, __ldg(f.ms[2] + nO));
             if (upd) {
-               const double mz = __ldg(f.md[2] + nO), my = __ldg(f.md[1] + nO), mx = __ldg(f.md[0] + nO);
+               const double mz = __ldg(f.md[2] + nO);
                HTR_UNROLL
-               for (int e = 0; e < nEq; e++) {
+               for (int e = 0; e < nEq; e++) ct[e] += mz*(Dz[e] - FzM[e]);
+            }
+            HTR_UNROLL
+            for (int e = 0; e < nEq; e++) FzM[e] = Dz[e];
+         }
+         HTR_UNROLL
+         for (int k = 0; k < 4; k++) gC[k] = gN[k];
+         {
+            double Dy[nEq];
+            if (faceAct) diffFaceStream<1>(Dy, HTR_DGET(ownD, ownE, 0, 1, 5, 6), HTR_DGET(ownD + DW, ownE + PW, 0, 1, 5, 6), __ldg(f.ms[1] + nO));
+            else { HTR_UNROLL for (int e = 0; e < nEq; e++) Dy[e] = 0.0; }
+            HTR_UNROLL
+            for (int e = 0; e < nEq; e++) sF[e*PNT + tid] = Dy[e];
+         }
+         double Dx[nEq];
+         if (faceAct) diffFaceStream<0>(Dx, HTR_DGET(ownD, ownE, 3, 2, 4, 6), HTR_DGET(ownD + 1, ownE + 1, 3, 2, 4, 6), __ldg(f.ms[0] + nO));
+         else { HTR_UNROLL for (int e = 0; e < nEq; e++) Dx[e] = 0.0; }
+         #undef HTR_DGET
+         __syncthreads();                                                          // B5: sF visible, the D data has been read
+         {
+            const double my = upd ? __ldg(f.md[1] + nO) : 0.0, mx = upd ? __ldg(f.md[0] + nO) : 0.0;
+            HTR_UNROLL
+            for (int e = 0; e < nEq; e++) {
+               const double DxM = __shfl_up_sync(0xffffffffu, Dx[e], 1);
+               if (upd) {
                   double v = ct[e];
-                  v += mz*(Dz[e] - FzM[e]);
-                  v += my*(Dy[e] - sF[e*PNT + tid - 32]);
-                  v += mx*(Dx[e] - DxM[e]);
+                  v += my*(sF[e*PNT + tid] - sF[e*PNT + tid - 32]);
+                  v += mx*(Dx[e] - DxM);
                   ct[e] = v;
                }
             }
          }
-         HTR_UNROLL
-         for (int e = 0; e < nEq; e++) FzM[e] = Dz[e];
-         HTR_UNROLL
-         for (int k = 0; k < 4; k++) gC[k] = gN[k];
       }
 
       // ---- (5) Conserved_t rows leave as contiguous spans; deferred cells keep their value -----------------
-      const bool deferred = bad3 || !okE;
+      const bool deferred = !okE;
       if (upd) {
          mask[((int64_t)p*f.n[1] + y)*f.n[0] + x] = deferred;
          if (deferred) *flag = 1;
@@ -666,7 +652,7 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
             }
          }
       }
-      badP = DIFF ? badC : false; badC = badN;
+      if (!DIFF) __syncthreads();      // without the D phase: the E data / sF of this plane have been read before the next plane is staged
    }
    #undef HTR_ZP
 }

@@ -16,6 +16,8 @@
 #include <cassert>
 #include <cmath>
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 
 enum legion_privilege_mode_stub { READ_ONLY = 1, READ_WRITE = 7, WRITE_ONLY = 0x10000002, WRITE_DISCARD = 0x10000002, REDUCE = 8 };
 
@@ -56,21 +58,37 @@ namespace Legion {
    template<> inline size_t Rect<1, coord_t>::volume() const { return size_t(hi.x - lo.x + 1); }
 
    struct Domain {
-      Rect<3> r3; Rect<1> r1;
-      Domain() {}
-      Domain(const Rect<3> &r) : r3(r) {}
-      operator Rect<3>() const { return r3; }
+      Rect<3> r3; Rect<1> r1; bool dense;
+      Domain() : dense(true) {}
+      Domain(const Rect<3> &r, bool d = true) : r3(r), dense(d) {}
+      operator Rect<3>() const {
+         if (!dense) { fprintf(stderr, "stub legion.h: Domain -> Rect<3> conversion of a SPARSE index space (Legion aborts here)\n"); abort(); }
+         return r3;
+      }
       operator Rect<1>() const { return r1; }
    };
 
-   struct IndexSpace { Rect<3> bounds; };
+   // An index space is a bounding rectangle plus a flag: the reference's ghost partitions are unions of shifted /
+   // wrapped pieces (src/prometeo_partitioner.rg:1239+), i.e. SPARSE -- converting such a domain to a Rect aborts in
+   // Legion, and so it does here (tests/test_adapter_gpu.py drives the adapter with sparse ghost regions).
+   struct IndexSpace { Rect<3> bounds; bool dense; IndexSpace() : dense(true) {} IndexSpace(const Rect<3> &b, bool d = true) : bounds(b), dense(d) {} };
    struct FieldSpace { unsigned id; };
    struct LogicalRegion {
       unsigned tree_id; unsigned long long index_space_id; unsigned is_tid; unsigned type_tag; unsigned field_space_id;
-      IndexSpace get_index_space() const { return IndexSpace(); }
+      const IndexSpace *stub_is;
+      LogicalRegion() : tree_id(0), index_space_id(0), is_tid(0), type_tag(0), field_space_id(0), stub_is(0) {}
+      IndexSpace get_index_space() const { return stub_is ? *stub_is : IndexSpace(); }
    };
+   // One field of a physical instance: base addresses global point (0,0,0), byte strides (Realm::AffineAccessor).
+   struct StubField { FieldID fid; void *base; coord_t s[3]; };
    struct PhysicalRegion {
-      LogicalRegion get_logical_region() const { return LogicalRegion(); }
+      IndexSpace is;
+      std::vector<StubField> fields;       // exactly the fields this region requirement names
+      LogicalRegion get_logical_region() const { LogicalRegion l; l.stub_is = &is; return l; }
+      const StubField *find(FieldID fid) const {
+         for (size_t i = 0; i < fields.size(); i++) if (fields[i].fid == fid) return &fields[i];
+         return 0;
+      }
    };
    struct Future {
       double v;
@@ -96,7 +114,7 @@ namespace Legion {
       void set_leaf(bool = true) {}
    };
    struct Runtime {
-      Domain get_index_space_domain(Context, const IndexSpace &is) { return Domain(is.bounds); }
+      Domain get_index_space_domain(Context, const IndexSpace &is) { return Domain(is.bounds, is.dense); }
       template<void (*F)(const Task*, const std::vector<PhysicalRegion>&, Context, Runtime*)>
       static void preregister_task_variant(const TaskVariantRegistrar&, const char*) {}
       template<typename R, R (*F)(const Task*, const std::vector<PhysicalRegion>&, Context, Runtime*)>
@@ -104,7 +122,13 @@ namespace Legion {
       static LayoutConstraintID preregister_layout(const LayoutConstraintRegistrar&) { return 0; }
    };
    template<typename T> class SumReduction {};
-   template<typename T> struct DeferredValue { T v; DeferredValue(T x = T()) : v(x) {} T* ptr() { return &v; } };
+   // GPU variants return a DeferredValue whose storage is device-visible; the stub keeps a caller-settable pointer
+   template<typename T> struct DeferredValue {
+      T v; T *p;
+      static T *&stub_storage() { static T *s = 0; return s; }       // test harness: device buffer for the result
+      DeferredValue(T x = T()) : v(x), p(stub_storage()) {}
+      T* ptr() { return p ? p : &v; }
+   };
    template<typename T, int N> struct DeferredBuffer {};
    template<int N> struct RectInDomainIterator {};
 
@@ -115,13 +139,23 @@ namespace Legion {
    struct FieldAccessor<PRIV, FT, 3, T, A> {
       char *base; coord_t sx, sy, sz;   // base addresses global point (0,0,0)
       FieldAccessor() : base(0), sx(0), sy(0), sz(0) {}
-      FieldAccessor(const PhysicalRegion&, FieldID) : base(0), sx(0), sy(0), sz(0) {}
-      FieldAccessor(void *b, coord_t sx_, coord_t sy_, coord_t sz_) : base((char*)b), sx(sx_), sy(sy_), sz(sz_) {}
+      Rect<3> bounds; bool bounded;
+      // the accessor of a field the region requirement does not name is a Legion runtime error
+      FieldAccessor(const PhysicalRegion &r, FieldID fid) : base(0), sx(0), sy(0), sz(0), bounds(r.is.bounds), bounded(true) {
+         const StubField *f = r.find(fid);
+         if (!f) { fprintf(stderr, "stub legion.h: field %u is not part of this physical region\n", fid); abort(); }
+         base = (char*)f->base; sx = f->s[0]; sy = f->s[1]; sz = f->s[2];
+      }
+      FieldAccessor(void *b, coord_t sx_, coord_t sy_, coord_t sz_) : base((char*)b), sx(sx_), sy(sy_), sz(sz_), bounded(false) {}
       FT& operator[](const Point<3, T> &p) const { return *(FT*)(base + p.x*sx + p.y*sy + p.z*sz); }
-      // Legion: pointer to r.lo and strides in units of field_size
+      // Legion: pointer to r.lo and strides in units of field_size; r must lie inside the instance
       FT* ptr(const Rect<3, T> &r, size_t strides[3], size_t field_size = sizeof(FT)) const {
+         if (bounded && (r.lo.x < bounds.lo.x || r.lo.y < bounds.lo.y || r.lo.z < bounds.lo.z ||
+                         r.hi.x > bounds.hi.x || r.hi.y > bounds.hi.y || r.hi.z > bounds.hi.z)) {
+            fprintf(stderr, "stub legion.h: ptr(rect) outside the bounds of the instance\n"); abort();
+         }
          strides[0] = sx/field_size; strides[1] = sy/field_size; strides[2] = sz/field_size;
-         return &(*this)[r.lo];
+         return (FT*)(base + r.lo.x*sx + r.lo.y*sy + r.lo.z*sz);
       }
    };
    template<int PRIV, typename FT, typename T, typename A>

@@ -1,0 +1,195 @@
+"""CPU tests that PIN the oracle (oracle/_ref: the reference's own headers compiled in place behind a stub legion.h)
+on every known-answer vector the reference's unit tests hold for the hot path:
+
+  unitTests/mixTest/mixTest.rg:130-169        AirMix thermodynamics, transport, kinetics at 750 K (printed to 7 digits)
+  unitTests/variablesTest/variablesTest.rg    rho, mu, lam, D_i, SoS, Conserved at 5000 K (14 digits), and the inverse
+  unitTests/chemTest/chemTest.rg:45-49        production rates and the state after one implicit step
+  unitTests/cflTest/cflTest.rg:83-113         the four branches of the spectral radius
+  unitTests/mathUtilsTest/CPPmathUtilsTest.cc LU solve (1e-12) and the Rosenbrock integrator (1e-6)
+
+The tolerances are the reference's own, or tighter where the golden is printed with enough digits.
+"""
+import numpy as np
+import pytest
+from oracle_lib import Oracle, alloc_fields
+
+R = 8.3144598
+
+
+def have_oracle(mix):
+    try:
+        Oracle(mix)
+        return True
+    except FileNotFoundError:
+        return False
+
+
+needs_air = pytest.mark.skipif(not have_oracle("AirMix"), reason="oracle/_ref not built")
+needs_cp = pytest.mark.skipif(not have_oracle("ConstPropMix"), reason="oracle/_ref not built")
+
+# unitTests/mixTest/AirMix.json: "XiRef": N2 0.78, O2 0.22
+MIXTEST_AIR = {"type": "AirMix", "LRef": 1.0, "PRef": 101325.0, "TRef": 300.0,
+               "XiRef": {"Species": [{"Name": "N2", "MolarFrac": 0.78}, {"Name": "O2", "MolarFrac": 0.22}]}}
+
+
+def refs(PRef, TRef, MixWRef, LRef=1.0):
+    rhoRef = PRef * MixWRef / (R * TRef)
+    return dict(rhoRef=rhoRef, eRef=PRef / rhoRef, uRef=np.sqrt(PRef / rhoRef), CpRef=R / MixWRef,
+                muRef=np.sqrt(PRef * rhoRef) * LRef, lamRef=np.sqrt(PRef * rhoRef) * LRef * R / MixWRef,
+                DiRef=np.sqrt(PRef / rhoRef) * LRef, wiRef=np.sqrt(PRef * rhoRef) / LRef)
+
+
+@needs_air
+def test_mixtest_airmix_all_goldens():
+    """unitTests/mixTest/mixTest.rg:130-169 (expected values) and :756-890 (checks, 1e-3).  The goldens are printed with
+    7 significant digits; the oracle reproduces every one of them to that precision."""
+    o = Oracle("AirMix"); o.init_mix(MIXTEST_AIR)
+    P, T = 101325.0, 750.0
+    MixWRef = 2.889018800000000e-02
+    q = refs(101325.0, 300.0, MixWRef)
+    r = o.mix_eval(P / 101325.0, T / 300.0, [0.2] * 5)
+    W = np.array([o.lib.htr_oracle_species_W(i) for i in range(5)])
+    assert np.allclose(W, [2 * 14.0067e-3, 2 * 15.9994e-3, 30.00610e-03, 14.0067e-03, 15.9994e-03], rtol=1e-12)
+    EMixW = 2.135186e-02
+    Erho = P * EMixW / (R * T)
+    tol = 1e-6          # 7 printed digits
+    def chk(got, exp, what):
+        assert abs(got / exp - 1.0) < tol, (what, got, exp)
+    chk(1.0 / np.sum(0.2 / W), EMixW, "MixW")
+    for i, e in enumerate([1.524403e-01, 1.334541e-01, 1.423168e-01, 3.048806e-01, 2.669082e-01]):
+        chk(r["Xi"][i], e, f"Xi[{i}]")
+    chk(r["rho"] * q["rhoRef"], Erho, "rho")
+    chk(r["cp"] * q["CpRef"], 1.206133e+03, "cp")
+    chk(r["h"] * q["eRef"], 1.100436e+07, "h")
+    chk(r["e"] * q["eRef"], 1.100436e+07 - P / Erho, "e")
+    chk(r["mu"] * q["muRef"], 3.723077e-05, "mu")
+    chk(r["lam"] * q["lamRef"], 6.736994e-02, "lam")
+    chk(r["gamma"], 1.476782e+00, "gamma")
+    chk(r["SoS"] * q["uRef"], 6.567317e+02, "SoS")
+    for i, e in enumerate([1.192983e-04, 1.174019e-04, 1.162986e-04, 1.820668e-04, 1.882347e-04]):
+        chk(r["Di"][i] * q["DiRef"], e, f"Di[{i}]")
+    for i, e in enumerate([3.413124e+07, 2.664566e+04, -3.578332e+07, -1.742776e+07, 1.905320e+07]):
+        chk(r["w"][i] * q["wiRef"], e, f"w[{i}]")
+    chk(r["dpde"] * q["rhoRef"], Erho * (1.476782e+00 - 1.0), "dpde")
+    for i, e in enumerate([5.206698e+06, 5.184248e+06, 3.742883e+06, -1.064452e+07, -2.029053e+06]):
+        chk(r["dpdrhoi"][i] * q["eRef"], e, f"dpdrhoi[{i}]")
+    for i, e in enumerate([4.812927e+05, 4.425045e+05, 3.505703e+06, 3.441706e+07, 1.617526e+07]):
+        chk(o.lib.htr_oracle_species_enthalpy(i, T / 300.0) * q["eRef"], e, f"hsp[{i}]")
+    # Newton inversion e -> T from a 5 % perturbed guess (mixTest.rg: GetTFromInternalEnergy check)
+    chk(r["T_from_e"], T / 300.0, "T(e)")
+    chk(r["MixW_Xi"], r["MixW"], "MixW(Xi)")
+
+
+def _unit_test_air_cfg():
+    """The mixture of variablesTest.rg / chemTest.rg: reference state from Y_O2 = 0.22, Y_N2 = 0.78."""
+    MixWRef = 1.0 / (0.78 / 28.0134e-3 + 0.22 / (2 * 15.999e-3))
+    cfg = {"type": "AirMix", "LRef": 1.0, "PRef": 101325.0, "TRef": 300.0,
+           "XiRef": {"Species": [{"Name": "O2", "MolarFrac": MixWRef * 0.22 / (2 * 15.999e-3)},
+                                 {"Name": "N2", "MolarFrac": MixWRef * 0.78 / 28.0134e-3}]}}
+    return cfg, refs(101325.0, 300.0, MixWRef)
+
+
+@needs_air
+def test_variablestest_goldens():
+    """unitTests/variablesTest/variablesTest.rg:56-72 (14-digit goldens), checks :119-200 with the reference's 1e-8:
+    UpdatePropertiesFromPrimitive, UpdateConservedFromPrimitive and back through UpdatePrimitiveFromConserved."""
+    cfg, q = _unit_test_air_cfg()
+    o = Oracle("AirMix"); o.init_mix(cfg)
+    P, T = 101325.0, 5000.0
+    Xi = np.array([0.4, 0.2, 0.15, 0.15, 0.1]); v = np.array([1.0, 2.0, 3.0])
+    f = alloc_fields(3, 2, 2, 5)
+    f["pressure"][...] = P / 101325.0
+    f["temperature"][...] = T / 300.0
+    f["MolarFracs"][...] = Xi
+    f["velocity"][...] = v / q["uRef"]
+    o.update_properties_from_primitive(f)
+    tol = 1e-8
+    assert np.all(np.abs(f["rho"] * q["rhoRef"] / 6.2899525132668e-02 - 1.0) < tol)
+    assert np.all(np.abs(f["mu"] * q["muRef"] / 1.2424432854120e-04 - 1.0) < tol)
+    assert np.all(np.abs(f["lam"] * q["lamRef"] / 2.4040406505225e-01 - 1.0) < tol)
+    eDi = np.array([2.5146942638910e-03, 2.4389378958326e-03, 2.4551032686824e-03, 3.6168376636972e-03, 3.9165741891924e-03])
+    assert np.all(np.abs(f["Di"] * q["DiRef"] / eDi - 1.0) < tol)
+    assert np.all(np.abs(f["SoS"] * q["uRef"] / 1.4518745895533e+03 - 1.0) < tol)
+    o.update_conserved_from_primitive(f)
+    eC = np.array([2.3342371515176e-02, 1.3331617683677e-02, 9.3760512904744e-03, 4.3766946590956e-03, 3.3329044209192e-03,
+                   1.8268107194243e-04, 3.6536214388485e-04, 5.4804321582728e-04, 5.3385045774457e+00])
+    assert np.all(np.abs(f["Conserved"] / eC - 1.0) < tol)
+    # and back, from the test's restart temperature Tres = 500 K as the Newton guess
+    f["pressure"][...] = 0.0; f["MolarFracs"][...] = 0.0; f["velocity"][...] = 0.0
+    f["temperature"][...] = 500.0 / 300.0
+    o.update_primitive_from_conserved(f)
+    assert np.all(np.abs(f["pressure"] * 101325.0 / P - 1.0) < tol)
+    assert np.all(np.abs(f["temperature"] * 300.0 / T - 1.0) < tol)
+    assert np.all(np.abs(f["MolarFracs"] / Xi - 1.0) < tol)
+    assert np.all(np.abs(f["velocity"] * q["uRef"] / v - 1.0) < tol)
+
+
+@needs_air
+def test_chemtest_goldens():
+    """unitTests/chemTest/chemTest.rg:45-49: AddChemistrySources (Eprod) and UpdateChemistry over 1e-6 s (Cres), both to
+    the reference's 1e-5."""
+    cfg, q = _unit_test_air_cfg()
+    o = Oracle("AirMix"); o.init_mix(cfg)
+    P, T = 101325.0, 5000.0
+    Yi = np.array([0.78, 0.22, 1.0e-60, 1.0e-60, 1.0e-60])
+    r = o.mix_eval(P / 101325.0, T / 300.0, Yi)
+    f = alloc_fields(2, 2, 2, 5)
+    f["pressure"][...] = P / 101325.0
+    f["temperature"][...] = T / 300.0
+    f["MassFracs"][...] = Yi
+    f["MolarFracs"][...] = r["Xi"]
+    f["rho"][...] = r["rho"]
+    f["Conserved"][..., :5] = r["rho"] * Yi
+    f["Conserved"][..., 8] = r["rho"] * r["e"]
+    o.add_chemistry_sources(f)
+    Eprod = np.array([-1.658328e-01, -1.445940e+03, 1.332770e-54, 1.658328e-01, 1.445940e+03, 0.0, 0.0, 0.0, 0.0])
+    got = f["Conserved_t"] * q["wiRef"]
+    err = np.where(Eprod != 0, (got - Eprod) / np.where(Eprod != 0, Eprod, 1.0), got - Eprod)
+    assert np.all(np.abs(err) < 1e-5), err.reshape(-1, 9)[0]
+    # implicit step.  The reference test does NOT clear Conserved_t in between (chemTest.rg:118-135): the production
+    # rates just added act as the frozen explicit part of the split right-hand side (Conserved_t_old = Conserved_t).
+    dt = 1e-6 * np.sqrt(101325.0 / q["rhoRef"]) / 1.0
+    o.update_chemistry(f, dt)
+    Cres = np.array([5.460212e-02, 1.296359e-02, 2.994386e-04, 1.502734e-05, 2.321006e-03, 0.0, 0.0, 0.0, 3.141423e+05])
+    got = f["Conserved"] * q["rhoRef"]
+    got[..., 8] *= q["eRef"]
+    err = np.where(Cres != 0, (got - Cres) / np.where(Cres != 0, Cres, 1.0), got - Cres)
+    assert np.all(np.abs(err) < 1e-5), err.reshape(-1, 9)[0]
+
+
+@needs_cp
+def test_cfltest_goldens():
+    """unitTests/cflTest/cflTest.rg:83-113: acoustic 11, momentum diffusion 40, energy diffusion 11.42857,
+    species diffusion 40 (1e-3)."""
+    o = Oracle("ConstPropMix")
+    o.init_mix({"type": "ConstPropMix", "gasConstant": 1.0, "gamma": 1.4, "prandtl": 0.71,
+                "viscosityModel": {"type": "Constant", "Visc": 0.0}})
+    f = alloc_fields(2, 2, 2, 1)
+    for k in ("dcsi_d", "deta_d", "dzet_d", "rho"):
+        f[k][...] = 1.0
+    f["MassFracs"][...] = 1.0; f["MolarFracs"][...] = 1.0
+    f["velocity"][...] = 1.0; f["SoS"][...] = 10.0
+    assert abs(o.max_spectral_radius(f) / 11.0 - 1.0) < 1e-3
+    f["velocity"][...] = 0.0
+    f["mu"][...] = 10.0
+    assert abs(o.max_spectral_radius(f) / 40.0 - 1.0) < 1e-3
+    f["mu"][...] = 0.0
+    f["lam"][...] = 10.0
+    assert abs(o.max_spectral_radius(f) / 11.42857 - 1.0) < 1e-3
+    f["lam"][...] = 0.0
+    f["Di"][...] = 10.0
+    assert abs(o.max_spectral_radius(f) / 40.0 - 1.0) < 1e-3
+
+
+@needs_air
+def test_mathutils_goldens():
+    """unitTests/mathUtilsTest/CPPmathUtilsTest.cc:6-55: LUdec<3> (1e-12) and Rosenbrock<3> on the stiff 3-equation
+    kinetics problem (1e-6)."""
+    o = Oracle("AirMix")
+    A = np.array([[4.0, 3.0, 0.0], [3.0, 4.0, -1.0], [0.0, -1.0, 4.0]])
+    b = np.array([24.0, 30.0, -24.0]); x = np.zeros(3)
+    o.lib.htr_oracle_lu3_solve(A.ctypes.data, b.ctypes.data, x.ctypes.data)
+    assert np.all(np.abs(x - np.array([3.0, 4.0, -5.0])) < 1e-12)
+    y = np.array([1.0, 1.0, 0.0])
+    o.lib.htr_oracle_rosenbrock3(y.ctypes.data, 1.0e-3, 25.0)
+    assert np.all(np.abs(1.0 - y / np.array([7.818640e-01, 1.218133e+00, -2.655799e-06])) < 1e-6)

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 import htr_solver_b200 as htr
 from htr_solver_b200 import synthetic
-from parity import oracle_for, host_state, to_device, rel_err, euler_scale, scaled_err, TOL_FLUX, TOL_CHEM
+from parity import oracle_for, host_state, to_device, rel_err, euler_scale, scaled_err, solver_tol_ok, TOL_FLUX, TOL_CHEM
 
 pytestmark = pytest.mark.gpu
 
@@ -183,6 +183,43 @@ def test_full_rhs(cfg, scheme, chem, kw):
         scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
         f["Conserved_t"][...] = ref
     e = scaled_err(got, f["Conserved_t"], scale)
+    assert e <= (TOL_CHEM if chem else TOL_FLUX), e
+
+
+@pytest.mark.parametrize("cfg,scheme,chem,n,kw", [
+    (synthetic.CONSTPROP_3DPERIODIC, "TENO", False, (128, 128, 128), {}),                       # BASELINE config C2 (3DPeriodic_TENO, 128^3)
+    (synthetic.CONSTPROP_3DPERIODIC, "Hybrid", False, (128, 128, 128), {"front": 0.3}),         # C2 with the hybrid switch live
+    (AIR, "Hybrid", True, (256, 256, 64), {"species_wave": 1.0}),                               # C4 cross-section (3DPeriodic_Air, 256^2 x 64)
+    (AIR, "Hybrid", True, (256, 256, 64), {"species_wave": 1.0, "front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5})],
+    ids=["C2-teno-128", "C2-hybrid-128", "C4-air-256x256x64", "C4-air-front-256x256x64"])
+def test_full_rhs_at_baseline_grid_sizes(cfg, scheme, chem, n, kw):
+    """htr_rhs against the reference's CPU tasks at the grid sizes BASELINE.json names (where the kernels run tens of
+    thousands of CTAs, several z chunks and every partial tile), not only on the small boxes of the other tests."""
+    from oracle_lib import Oracle
+    try:
+        o = Oracle(cfg["type"], omp=True, kind="reference")      # the -O3 OpenMP build of the same sources: minutes -> seconds
+    except FileNotFoundError:
+        o = oracle_for(cfg)
+    o.init_mix(cfg)
+    f = host_state(o, n, cfg, **kw)
+    _sensors(o, f)
+    diffusion = cfg is AIR
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    o.rhs(f, scheme, diffusion=diffusion, chemistry=chem, RK0=1.0, RK1=0.0, dt=1e-3)
+    fl.t["Conserved_t"].fill_(7.0)
+    s.UpdateDerivatives(fl, scheme, diffusion=diffusion, chemistry=chem, RK_coeffs=(1.0, 0.0), deltaTime=1e-3)
+    got = fl.download(["Conserved_t"])["Conserved_t"]
+    scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
+    if chem:
+        ref = f["Conserved_t"].copy()
+        f["Conserved_t"][...] = 0.0
+        o.add_chemistry_sources(f)
+        scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
+        f["Conserved_t"][...] = ref
+    e = scaled_err(got, f["Conserved_t"], scale)
+    smooth = float(np.mean(f["shockSensorX"])) if scheme == "Hybrid" else None
+    print(f"{cfg['type']} {scheme} {n}: max scaled error {e:.3e}, by max|ref| {rel_err(got, f['Conserved_t']):.3e}, smooth fraction {smooth}")
     assert e <= (TOL_CHEM if chem else TOL_FLUX), e
 
 
@@ -514,6 +551,10 @@ def test_time_step(cfg, scheme, chem, kw):
         for k in names:
             e = rel_err(got[k], f[k])
             assert e <= TOL_CHEM, (step, k, e)
+        # the reference's own acceptance rule for a solver test (solverTests/testAll.py:23-36), point-wise, on the
+        # fields its restart files hold (src/prometeo.rg:144-152)
+        for k in ("pressure", "temperature", "velocity", "MolarFracs", "rho"):
+            assert solver_tol_ok(got[k], f[k]), (step, k, float(np.abs(got[k] - f[k]).max()))
     # the step moved the state (the comparison is not between two copies of the initial condition)
     assert rel_err(f["Conserved"], f["Conserved_old"]) > 1e-4
 
