@@ -116,6 +116,7 @@ def load_library(mix, variant=""):
     L.htr_rhs_parts.argtypes = [i, i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
     L.htr_probe_fp64.argtypes = [d, vp, vp]
+    L.htr_chemistry_failures_on.argtypes = [vp]
     assert L.htr_mixture_name().decode() == mix
     _LIBS[key] = L
     return L
@@ -270,7 +271,7 @@ class Solver:
     def UpdateChemistry(self, fl, Integrator_deltaTime, tile=None):
         t, _ = self._rects(fl, tile, None)
         self._check(self.L.htr_update_chemistry(C.byref(fl.struct()), t, Integrator_deltaTime, self._stream()), "htr_update_chemistry")
-        nfail = self.L.htr_chemistry_failures()
+        nfail = self.L.htr_chemistry_failures_on(self._stream())
         if nfail:
             raise HTRError(f"implicit chemistry did not converge in {nfail} cells")
 

@@ -158,7 +158,27 @@ static cudaError_t launchFlux(const htr_fluid &f, const htr_rect &tile, const ht
    return cudaGetLastError();
 }
 
-static int g_num_sms = 0;
+// ---- per-device library state -------------------------------------------------------------------------------
+// One Legion rank drives several GPUs (one GPU processor per device, src/prometeo_mapper.cc:231-262), so everything the
+// library caches is keyed on the CURRENT device: the "mixture loaded" flag (the __constant__ block itself is per
+// device already), the SM count, the cudaFuncSetAttribute guards, the scratch buffers and the host-pipeline streams.
+constexpr int HTR_MAX_DEVICES = 64;
+static inline int curDev() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < HTR_MAX_DEVICES) ? d : 0; }
+static int g_num_sms[HTR_MAX_DEVICES] = {};
+static int numSMs() {
+   const int d = curDev();
+   if (g_num_sms[d] == 0 &&
+       (cudaDeviceGetAttribute(&g_num_sms[d], cudaDevAttrMultiProcessorCount, d) != cudaSuccess || g_num_sms[d] <= 0)) g_num_sms[d] = 148;
+   return g_num_sms[d];
+}
+// true once per (device, slot): the caller then raises the dynamic shared-memory limits of its kernels on that device
+static bool firstUseOnDevice(int slot) {
+   static bool done[8][HTR_MAX_DEVICES] = {};
+   const int d = curDev();
+   if (done[slot][d]) return false;
+   done[slot][d] = true;
+   return true;
+}
 
 template<int dir, int KIND, int SCHEME>
 static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
@@ -167,12 +187,8 @@ static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const 
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
    const int C[3] = {FB::X - (dir == 0), FB::Y - (dir == 1), FB::Z - (dir == 2)};
    const unsigned gx = (unsigned)((n[0] + C[0] - 1)/C[0]), gy = (unsigned)((n[1] + C[1] - 1)/C[1]), gz = (unsigned)((n[2] + C[2] - 1)/C[2]);
-   if (g_num_sms == 0) {
-      int dev = 0; cudaGetDevice(&dev);
-      if (cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || g_num_sms <= 0) g_num_sms = 148;
-   }
-   const uint64_t total = (uint64_t)gx*gy*gz;
-   const unsigned grid = (unsigned)(total < (uint64_t)g_num_sms ? total : (uint64_t)g_num_sms);
+   const uint64_t total = (uint64_t)gx*gy*gz, sms = (uint64_t)numSMs();
+   const unsigned grid = (unsigned)(total < sms ? total : sms);
    dim3 block(FB::X, FB::Y, FB::Z);
    masked_flux_kernel<dir, KIND, SCHEME><<<grid, block, 0, st>>>(f, tile, B, ep, mask, flag, gx, gy, gz);
    return cudaGetLastError();
@@ -236,12 +252,10 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    int *flags = reinterpret_cast<int*>(scratch);      // cells deferred by: [0] Euler z, [1] Euler xy, [2] diffusion z, [3] diffusion xy
    uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
    { cudaError_t e = cudaMemsetAsync(flags, 0, 16, st); if (e != cudaSuccess) return e; }
-   static bool attr = false;
-   if (!attr) {
+   if (firstUseOnDevice(HY ? 0 : 1)) {
       cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
       cudaFuncSetAttribute(fast::euler_z_chem_kernel<HY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ZT_SMEM);
       cudaFuncSetAttribute(fast::euler_xy_bulk_kernel<TY, HY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::XYB<TY>::SMEM);
-      attr = true;
    }
    if (parts & PART_EZ) {
       dim3 grid((unsigned)((n[2] + fast::ZT_Z - 2)/(fast::ZT_Z - 1)), (unsigned)((n[0] + fast::ZT_X - 1)/fast::ZT_X), (unsigned)n[1]);
@@ -275,21 +289,17 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
    int *flags = reinterpret_cast<int*>(scratch);
    uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
    const EulerParams ep = {0, 0, 0};
-   static bool attr = false;
-   if (!attr) {
+   if (firstUseOnDevice(2)) {
       cudaFuncSetAttribute(fast::diffusion_bulk_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<2, TJ>::SMEM);
       cudaFuncSetAttribute(fast::diffusion_bulk_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<1, TJ>::SMEM);
-      attr = true;
    }
    cudaError_t e;
    if (!g_bulk_diffusion) {
       // default: cooperative staging (htr_fast.cuh).  Measured on B200 (profiles/r1_v8_*): the bulk-copy variant below
       // needs ~90 row copies of 0.3-2.6 KB per CTA and is TMA-issue bound (Dz 3.2 vs 1.9 ms, Dxy 4.2 vs 3.3 ms at 256^3).
-      static bool attr2 = false;
-      if (!attr2) {
+      if (firstUseOnDevice(3)) {
          cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
          cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
-         attr2 = true;
       }
       dim3 gz((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
       if (parts & PART_DZ) {
@@ -324,7 +334,8 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
 
 // ---- z-marching two-pass form (htr_march.cuh) ---------------------------------------------------
 // htr_set_option("march", m): bit 0 = euler_z_march_kernel instead of fast::euler_z_chem_kernel, bit 1 = plane_march_kernel
-// instead of the three staged kernels euler_xy / diffusion_z / diffusion_xy.  Default 1: measured on B200 at 512^3 AirMix
+// instead of the three staged kernels euler_xy / diffusion_z / diffusion_xy, bit 2 (without bit 1) = plane_march_kernel
+// without its diffusion phase instead of euler_xy only.  Default 1: measured on B200 at 512^3 AirMix
 // (profiles/r2_*): Euler-z march 14.4 ms vs 15.7 ms staged; plane march 60.5 ms vs 13.5 + 13.6 + 23.0 ms staged (16 warps per
 // SM at 112 KB of shared memory per CTA leave its load latency exposed: issue slots 25 % busy vs 36-45 %).
 static int g_march = 1;
@@ -396,11 +407,9 @@ static cudaError_t launchMarch(bool chem, bool diffusion, const htr_fluid &f, co
    uint8_t *maskZ = scratch + 16, *maskP = maskZ + n[0]*n[1]*n[2];
    cudaError_t e;
    if ((e = cudaMemsetAsync(flags, 0, 16, st)) != cudaSuccess) return e;
-   static bool attr = false;
-   if (!attr) {
-      cudaFuncSetAttribute(march::plane_march_kernel<HY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march::PM_SMEM);
-      cudaFuncSetAttribute(march::plane_march_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march::PM_SMEM);
-      attr = true;
+   if (firstUseOnDevice(HY ? 4 : 5)) {
+      cudaFuncSetAttribute(march::plane_march_kernel<HY, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march::PLay<true>::SMEM);
+      cudaFuncSetAttribute(march::plane_march_kernel<HY, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)march::PLay<false>::SMEM);
    }
    if (parts & PART_EZ) {
       int kch = g_march_kz < 6 ? 6 : g_march_kz;
@@ -415,8 +424,8 @@ static cudaError_t launchMarch(bool chem, bool diffusion, const htr_fluid &f, co
       int kch = g_march_kp < 1 ? 1 : g_march_kp;
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + 6)/7), (unsigned)((n[2] + kch - 1)/kch));
       dim3 block(32, 8, 1);
-      if (diffusion) march::plane_march_kernel<HY, true><<<grid, block, march::PM_SMEM, st>>>(u, maskP, flags + 1, kch);
-      else           march::plane_march_kernel<HY, false><<<grid, block, march::PM_SMEM, st>>>(u, maskP, flags + 1, kch);
+      if (diffusion) march::plane_march_kernel<HY, true><<<grid, block, march::PLay<true>::SMEM, st>>>(u, maskP, flags + 1, kch);
+      else           march::plane_march_kernel<HY, false><<<grid, block, march::PLay<false>::SMEM, st>>>(u, maskP, flags + 1, kch);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st)) != cudaSuccess) return e;
       if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st)) != cudaSuccess) return e;
@@ -754,24 +763,34 @@ using namespace htr;
 #endif
 #endif
 
-static bool g_mix_loaded = false;
+static bool g_mix_loaded_dev[HTR_MAX_DEVICES] = {};
+#define g_mix_loaded g_mix_loaded_dev[curDev()]
 static bool g_no_fast = false;          // htr_set_option("fast", 0): per-task kernels only (A/B testing)
 
 // Device scratch owned by the library (mask bytes of the fast path).  One buffer per stream that ever
 // asked, grown on demand; growth synchronises the device once.
-struct Scratch { cudaStream_t st; void *p; size_t bytes; };
-static Scratch g_scratch[16];
+struct Scratch { int dev; cudaStream_t st; void *p; size_t bytes; };
+constexpr int HTR_NSCRATCH = 64;
+static Scratch g_scratch[HTR_NSCRATCH];
 static int g_nscratch = 0;
 static void *scratchFor(size_t bytes, cudaStream_t st) {
+   const int dev = curDev();
    int k = -1;
-   for (int i = 0; i < g_nscratch; i++) if (g_scratch[i].st == st) { k = i; break; }
+   for (int i = 0; i < g_nscratch; i++) if (g_scratch[i].dev == dev && g_scratch[i].st == st) { k = i; break; }
    if (k < 0) {
-      if (g_nscratch == 16) k = 0; else { k = g_nscratch++; g_scratch[k] = {st, nullptr, 0}; }
-      if (g_scratch[k].st != st) { cudaDeviceSynchronize(); cudaFree(g_scratch[k].p); g_scratch[k] = {st, nullptr, 0}; }
+      if (g_nscratch < HTR_NSCRATCH) { k = g_nscratch++; g_scratch[k] = {dev, st, nullptr, 0}; }
+      else {
+         // table full: recycle an entry of THIS device (its buffer may still be in use by queued work: drain that stream first)
+         for (int i = 0; i < g_nscratch; i++) if (g_scratch[i].dev == dev) { k = i; break; }
+         if (k < 0) return nullptr;
+         cudaStreamSynchronize(g_scratch[k].st);
+         g_scratch[k].st = st;
+      }
    }
    Scratch &s = g_scratch[k];
    if (s.bytes < bytes) {
-      if (s.p) { cudaDeviceSynchronize(); cudaFree(s.p); s.p = nullptr; s.bytes = 0; }
+      // only work queued on this stream can still read the old buffer
+      if (s.p) { cudaStreamSynchronize(st); cudaFree(s.p); s.p = nullptr; s.bytes = 0; }
       if (cudaMalloc(&s.p, bytes) != cudaSuccess) { s.p = nullptr; return nullptr; }
       s.bytes = bytes;
    }
@@ -885,7 +904,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
-   if (strcmp(name, "march") == 0) { if (value < 0 || value > 3) return HTR_EINVAL; g_march = value; return HTR_OK; }
+   if (strcmp(name, "march") == 0) { if (value < 0 || value > 7) return HTR_EINVAL; g_march = value; return HTR_OK; }
    if (strcmp(name, "march_kz") == 0) { if (value < 1) return HTR_EINVAL; g_march_kz = value; return HTR_OK; }
    if (strcmp(name, "march_kp") == 0) { if (value < 1) return HTR_EINVAL; g_march_kp = value; return HTR_OK; }
    return HTR_EINVAL;
@@ -1045,6 +1064,16 @@ int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double dt, vo
 
 /* number of cells whose implicit integration hit the iteration caps since the last call
  * (the reference asserts, src/Utils/math_utils.hpp:233,240); synchronises the device */
+int htr_chemistry_failures(void);
+int htr_mixture_loaded(void) { return g_mix_loaded ? 1 : 0; }
+
+/* the same, ordered after the work queued on `stream` (cudaMemcpyFromSymbol alone only orders against the legacy default
+ * stream, not against non-blocking streams such as PyTorch side streams or Realm task streams) */
+int htr_chemistry_failures_on(void *stream) {
+   if (cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) return -1;
+   return htr_chemistry_failures();
+}
+
 int htr_chemistry_failures(void) {
    int n = 0, zero = 0;
    if (cudaMemcpyFromSymbol(&n, d_chem_failures, sizeof(int)) != cudaSuccess) return -1;
@@ -1191,11 +1220,17 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
       march::UF u;
       if (g_march && makeUniform(rf, rt, rb, scheme == HTR_SCHEME_HYBRID, chemistry != 0, diffusion != 0, u)) {
          // z-marching kernels (htr_march.cuh); parts: PART_EZ = Euler-z pass, PART_EXY = plane pass (Euler y, x + diffusion)
-         const int mparts = (g_march & 2) ? parts : (parts & PART_EZ);
+         const bool planeAll = (g_march & 2) != 0, planeEuler = !planeAll && (g_march & 4) != 0;
+         const int mparts = (planeAll || planeEuler) ? (parts & (PART_EZ | PART_EXY)) : (parts & PART_EZ);
+         const bool mdiff = diffusion != 0 && planeAll;
          const cudaError_t em = (scheme == HTR_SCHEME_HYBRID)
-            ? launchMarch<HTR_SCHEME_HYBRID>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, mparts)
-            : launchMarch<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, diffusion != 0, *f, *tile, *bounds, u, ep, scratch, st, mparts);
-         if (em != cudaSuccess || (g_march & 2)) return cuerr(em);
+            ? launchMarch<HTR_SCHEME_HYBRID>(chemistry != 0, mdiff, *f, *tile, *bounds, u, ep, scratch, st, mparts)
+            : launchMarch<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, mdiff, *f, *tile, *bounds, u, ep, scratch, st, mparts);
+         if (em != cudaSuccess || planeAll) return cuerr(em);
+         if (planeEuler) {                // diffusion through the staged kernels (flags [2], [3] were cleared by launchMarch)
+            if (diffusion) return cuerr(launchFastDiffusion(*f, *tile, *bounds, rf, rt, rb, scratch, st, parts));
+            return HTR_OK;
+         }
          parts &= ~PART_EZ;               // the staged kernels do the rest
       }
       cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
@@ -1296,7 +1331,8 @@ static void *cellPtr(const htr_acc &a, const htr_rect &t) {
 // and 8 planes, and the call takes about max(H2D, D2H) of the whole state plus that lag.
 constexpr int PIPE_MAXSLABS = 64;
 struct HostPipe { cudaStream_t up, down; cudaEvent_t evUp[PIPE_MAXSLABS], evR[PIPE_MAXSLABS + 2], evStart, evDone; bool ok; };
-static HostPipe g_pipe = {};
+static HostPipe g_pipe_dev[HTR_MAX_DEVICES] = {};
+#define g_pipe g_pipe_dev[curDev()]
 static bool pipeInit() {
    if (g_pipe.ok) return true;
    if (cudaStreamCreateWithFlags(&g_pipe.up, cudaStreamNonBlocking) != cudaSuccess) return false;

@@ -40,6 +40,9 @@
 #ifndef HTR_MP_MINB
 #define HTR_MP_MINB 2
 #endif
+#ifndef HTR_ME_MINB
+#define HTR_ME_MINB 3
+#endif
 
 namespace htr {
 namespace march {
@@ -235,17 +238,21 @@ constexpr int DW = 33, DR = 9, NCD = DW*DR;           // diffusion box: columns 
 constexpr int PNT = 256;
 constexpr int NG = 7;                                  // staged derivatives: dUdX dVdX dUdY dVdY dUdZ dVdZ dWdZ
 // shared-memory map (doubles).  R1 is time-shared: the E data of a plane is dead when its D data is staged.
-constexpr int OFF_V = 0;                               // [3][NCE*3] velocity ring, AoS
-constexpr int OFF_R1 = 3*NCE*3;
 constexpr int E_RHO = 0, E_P = NCE, E_H = 2*NCE, E_Y = 3*NCE, E_END = NCE*(3 + nSpec);
 constexpr int D_RHO = 0, D_MU = NCD, D_LAM = 2*NCD, D_T = 3*NCD, D_X = 4*NCD, D_DI = D_X + NCD*nSpec,
               D_RY = D_DI + NCD*nSpec, D_G = D_RY + NCD*nSpec, D_END = D_G + NG*NCD;
-constexpr int OFF_SO = E_END;                          // [8][32*nEq] output rows: beyond the E data, inside the (dead) D data
-constexpr int OFF_SB = OFF_SO + 8*32*nEq;              // sensor bytes of the stencil box (E phase only), inside the D data
-constexpr int OFF_SF = D_END;                          // [nEq][PNT] y-face exchange, aliases nothing
-constexpr int R1_DBL = OFF_SF + nEq*PNT;
-static_assert(OFF_SB + 2*512/8 <= D_END, "sensor bytes must fit inside the time-shared region");
-constexpr size_t PM_SMEM = sizeof(double)*(OFF_R1 + R1_DBL) + 2*PNT;
+template<bool DIFF> struct PLay {
+   static constexpr int NV = DIFF ? 3 : 1;                // velocity planes resident (ring p-1, p, p+1 | plane p)
+   static constexpr int OFF_R1 = NV*NCE*3;
+   // with diffusion: output rows beyond the E data, inside the (dead) D data; without: over the (dead) E data
+   static constexpr int OFF_SO = DIFF ? E_END : 0;
+   static constexpr int OFF_SB = DIFF ? E_END + 8*32*nEq : E_END;          // sensor bytes of the stencil box (E phase only)
+   static constexpr int OFF_SF = DIFF ? D_END : E_END + 2*512/8;            // [nEq][PNT] y-face exchange, aliases nothing
+   static constexpr int R1_DBL = OFF_SF + nEq*PNT;
+   static constexpr size_t SMEM = sizeof(double)*(OFF_R1 + R1_DBL) + 2*PNT;
+   static_assert(!DIFF || OFF_SB + 2*512/8 <= D_END, "sensor bytes must fit inside the time-shared region");
+   static_assert(DIFF || 8*32*nEq <= E_END, "output rows must fit over the E data");
+};
 
 // Diffusion flux of the face between cells P and Q = P + 1 along dir (Std_node).  P(v), Q(v) return operand v of the
 // cell: 0 rho, 1 mu, 2 lam, 3 T, 4..6 velocity, 7.. X_i, then D_i, then rho Y_i, then the four transverse derivatives
@@ -333,15 +340,17 @@ HTR_DEV void zFaceDerivs(double *g, const double *__restrict__ v, const int vi, 
 }
 
 template<bool HYBRID, bool DIFF>
-__global__ void __launch_bounds__(PNT, HTR_MP_MINB)
+__global__ void __launch_bounds__(PNT, DIFF ? HTR_MP_MINB : HTR_ME_MINB)
 plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ flag, const int kch) {
+   using L = PLay<DIFF>;
+   constexpr int OFF_SO = L::OFF_SO;
    extern __shared__ double smem[];
-   double *sV = smem + OFF_V;
-   double *R1 = smem + OFF_R1;
-   double *sF = R1 + OFF_SF;
-   uint8_t *sSx = reinterpret_cast<uint8_t*>(R1 + OFF_SB);
+   double *sV = smem;
+   double *R1 = smem + L::OFF_R1;
+   double *sF = R1 + L::OFF_SF;
+   uint8_t *sSx = reinterpret_cast<uint8_t*>(R1 + L::OFF_SB);
    uint8_t *sSy = sSx + 512;
-   uint8_t *sHave = reinterpret_cast<uint8_t*>(R1 + R1_DBL);
+   uint8_t *sHave = reinterpret_cast<uint8_t*>(R1 + L::R1_DBL);
    uint8_t *sDef = sHave + PNT;
 
    const int i = threadIdx.x, j = threadIdx.y, tid = j*32 + i;
@@ -438,10 +447,10 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
 
    #pragma unroll 1
    for (int p = z0; p <= z1; p++) {
-      const int k3 = (p - z0)%3;
+      const int k3 = DIFF ? (p - z0)%3 : 0;
       const double *vm = sV + k3*(NCE*3);                           // plane p-1
-      const double *vc = sV + ((k3 + 1)%3)*(NCE*3);                 // plane p
-      double *vn = sV + ((k3 + 2)%3)*(NCE*3);                       // plane p+1
+      const double *vc = DIFF ? sV + ((k3 + 1)%3)*(NCE*3) : sV;     // plane p
+      double *vn = DIFF ? sV + ((k3 + 2)%3)*(NCE*3) : sV;           // plane p+1
       const int zo = HTR_ZP(p), zn = HTR_ZP(p + 1);
       const int nO = nOwn + zo;
 
@@ -460,7 +469,7 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
             if (HYBRID) { sSx[be] = __ldg(f.sens[0] + n); sSy[be] = __ldg(f.sens[1] + n); }
          }
       }
-      if (DIFF) stageV(vn, zn); else stageV(sV + ((k3 + 1)%3)*(NCE*3), zo);
+      if (DIFF) stageV(vn, zn); else stageV(sV, zo);
       __syncthreads();                                                             // B1
 
       // ---- (2) Euler y face (published through sF), Euler x face (registers) ------------------------------------

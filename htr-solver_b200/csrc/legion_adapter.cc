@@ -9,7 +9,9 @@
 // unpacks its PhysicalRegions into affine accessors and calls one htr_* function; no numerics here.
 // Region / field order per task: src/prometeo_rhs.cu:108-131,:247-269,:409-425,:540-566,
 // src/prometeo_sensor.cu, src/prometeo_chem.cu, src/prometeo_variables.cu, src/prometeo_cfl.cu:92-110.
-// Compile-checked here against oracle/stub/legion.h (Legion itself is not available): `make -C oracle adapter`.
+// Legion itself is not available here: the adapter is compiled against oracle/stub/legion.h (`make -C oracle adapter`) and
+// EXECUTED against that stub by tests/test_adapter_gpu.py (oracle/adapter_driver.cc builds the PhysicalRegions of every
+// task the way the reference's region requirements list them, with sparse ghost regions); it has never run inside Legion.
 #include "legion.h"
 using namespace Legion;
 #include "prometeo_rhs.hpp"
@@ -22,20 +24,22 @@ using namespace Legion;
 namespace {
 typedef const std::vector<PhysicalRegion> Regions;
 
+// Every field is addressed through the DENSE rectangle of the written region (the task's execution domain): the ghost
+// regions are unions of shifted / wrapped pieces (src/prometeo_partitioner.rg:1239+), their domains are sparse and must
+// never be converted to a Rect (Legion aborts) -- the reference indexes ghost accessors by point for the same reason.
+// All fields of a tile live in one instance that contains the tile, so ptr(tile) is valid for each of them.
 struct Unpacker {
-   Regions &regions; Context ctx; Runtime *runtime;
-   Rect<3> domain(int reg) const {
-      return runtime->get_index_space_domain(ctx, regions[reg].get_logical_region().get_index_space());
-   }
+   Regions &regions; Rect<3> tile;
+   Unpacker(Regions &r, int written, Context ctx, Runtime *runtime) : regions(r),
+      tile(runtime->get_index_space_domain(ctx, r[written].get_logical_region().get_index_space())) {}
    // base pointer of global point (0,0,0) + byte strides out of Legion's affine accessor
    template<typename ACC, typename FT> htr_acc get(int reg, FieldID fid) const {
       const ACC a(regions[reg], fid);
-      const Rect<3> r = domain(reg);
       size_t s[3];
-      FT *p = a.ptr(r, s);                     // pointer to r.lo, strides in elements of FT
+      FT *p = a.ptr(tile, s);                  // pointer to tile.lo, strides in elements of FT
       htr_acc o;
       for (int i = 0; i < 3; i++) o.stride[i] = (int64_t)(s[i]*sizeof(FT));
-      o.base = (char*)p - (r.lo.x*o.stride[0] + r.lo.y*o.stride[1] + r.lo.z*o.stride[2]);
+      o.base = (char*)p - (tile.lo.x*o.stride[0] + tile.lo.y*o.stride[1] + tile.lo.z*o.stride[2]);
       return o;
    }
    template<typename FT> htr_acc ro(int reg, FieldID fid) const { return get<AccessorRO<FT, 3>, FT>(reg, fid); }
@@ -46,11 +50,19 @@ struct Unpacker {
 htr_rect toRect(const Rect<3> &r) { return htr_rect{{r.lo.x, r.lo.y, r.lo.z}, {r.hi.x, r.hi.y, r.hi.z}}; }
 htr_fluid emptyFluid() { htr_fluid f; memset(&f, 0, sizeof(f)); return f; }
 void ok(int rc) { assert(rc == HTR_OK); (void)rc; }
-void *taskStream() { return 0; }     // Realm's per-task stream (default-stream hijack, src/prometeo_rhs.cu:146)
+// The stream the task's work must be ordered on.  With Realm's CUDA runtime hijack every launch on the default stream is
+// redirected to the task's stream (what the reference relies on, src/prometeo_rhs.cu:146); without it the task stream has
+// to be asked for.
+void *taskStream() {
+#ifdef REALM_USE_CUDART_HIJACK
+   return 0;
+#else
+   return (void*)Realm::Cuda::get_task_cuda_stream();
+#endif
+}
 
-void loadMix(const Mix &m) {         // args.mix is byte-identical to the library's parameter block
-   static bool done = false;
-   if (!done) { ok(htr_set_mixture(&m, sizeof(Mix))); done = true; }
+void loadMix(const Mix &m) {         // args.mix is byte-identical to the library's parameter block; once per DEVICE
+   if (!htr_mixture_loaded()) ok(htr_set_mixture(&m, sizeof(Mix)));
 }
 
 // direction-dependent members of htr_fluid and field ids (src/prometeo_rhs.cc:1100-1200 FID_nType etc.)
@@ -66,10 +78,12 @@ const DirFields DIR[3] = {
 constexpr int dirIndex(direction d) { return d == Xdir ? 0 : (d == Ydir ? 1 : 2); }
 
 // fields every Euler task reads from regions[0] (EulerGhost)
-void eulerGhost(htr_fluid &f, const Unpacker &u, bool teno) {
+// (MassFracs comes with regions[0] for the Hybrid and SkewSymmetric tasks, with regions[1] for the TENO tasks:
+// src/prometeo_rhs.cc:53 vs :177 -- asking regions[0] for it there is a Legion runtime error)
+void eulerGhost(htr_fluid &f, const Unpacker &u, bool teno, int massFracsRegion = 0) {
    f.Conserved = u.ro<VecNEq>(0, FID_Conserved);
    f.rho       = u.ro<double>(0, FID_rho);
-   f.MassFracs = u.ro<VecNSp>(0, FID_MassFracs);
+   f.MassFracs = u.ro<VecNSp>(massFracsRegion, FID_MassFracs);
    f.velocity  = u.ro<Vec3>(0, FID_velocity);
    f.pressure  = u.ro<double>(0, FID_pressure);
    if (teno) {
@@ -86,7 +100,7 @@ template<direction dir>
 void UpdateUsingHybridEulerFluxTask<dir>::gpu_base_impl(const Args &args, Regions &regions,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 4);
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 3, ctx, runtime);
    const DirFields &D = DIR[dirIndex(dir)];
    htr_fluid f = emptyFluid();
    eulerGhost(f, u, true);
@@ -95,7 +109,7 @@ void UpdateUsingHybridEulerFluxTask<dir>::gpu_base_impl(const Args &args, Region
    f.*D.nType  = u.ro<int>(2, D.fNType);
    f.Conserved_t = u.rw<VecNEq>(3, FID_Conserved_t);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(3)), B = toRect(args.Fluid_bounds);
+   const htr_rect tile = toRect(u.tile), B = toRect(args.Fluid_bounds);
    double dt = 0.0;
 #if (nSpec > 1)
    dt = futures[0].get_result<double>();
@@ -113,16 +127,15 @@ template<direction dir, class Op>
 void UpdateUsingTENOEulerFluxTask<dir, Op>::gpu_base_impl(const Args &args, Regions &regions,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 4);
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 3, ctx, runtime);
    const DirFields &D = DIR[dirIndex(dir)];
    htr_fluid f = emptyFluid();
-   eulerGhost(f, u, true);
-   f.MassFracs = u.ro<VecNSp>(1, FID_MassFracs);     // the TENO tasks request MassFracs with regions[1] (src/prometeo_rhs.cu:259)
+   eulerGhost(f, u, true, 1);
    f.*D.m_e   = u.ro<double>(1, D.fMe);
    f.*D.nType = u.ro<int>(2, D.fNType);
    f.Conserved_t = u.rw<VecNEq>(3, FID_Conserved_t);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(3)), B = toRect(args.Fluid_bounds);
+   const htr_rect tile = toRect(u.tile), B = toRect(args.Fluid_bounds);
    double dt = 0.0;
 #if (nSpec > 1)
    dt = futures[0].get_result<double>();
@@ -136,7 +149,7 @@ void UpdateUsingSkewSymmetricEulerFluxTask<dir>::gpu_base_impl(const Args &args,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 4);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 3, ctx, runtime);
    const DirFields &D = DIR[dirIndex(dir)];
    htr_fluid f = emptyFluid();
    eulerGhost(f, u, false);
@@ -144,7 +157,7 @@ void UpdateUsingSkewSymmetricEulerFluxTask<dir>::gpu_base_impl(const Args &args,
    f.*D.m_e   = u.ro<double>(2, D.fMe);
    f.Conserved_t = u.rw<VecNEq>(3, FID_Conserved_t);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(3)), B = toRect(args.Fluid_bounds);
+   const htr_rect tile = toRect(u.tile), B = toRect(args.Fluid_bounds);
    ok(htr_euler_flux(HTR_SCHEME_SKEWSYMMETRIC, dirIndex(dir), &f, &tile, &B, 1.0, 0.0, 0.0, taskStream()));
 }
 
@@ -154,7 +167,7 @@ void UpdateUsingDiffusionFluxTask<dir>::gpu_base_impl(const Args &args, Regions 
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 5);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 4, ctx, runtime);
    const int d = dirIndex(dir), d1 = dirIndex(getT1(dir)), d2 = dirIndex(getT2(dir));
    htr_fluid f = emptyFluid();
    f.Conserved   = u.ro<VecNEq>(0, FID_Conserved);
@@ -170,7 +183,7 @@ void UpdateUsingDiffusionFluxTask<dir>::gpu_base_impl(const Args &args, Regions 
    f.*DIR[d].m_d   = u.ro<double>(3, DIR[d].fMd);
    f.Conserved_t = u.rw<VecNEq>(4, FID_Conserved_t);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(4)), B = toRect(args.Fluid_bounds);
+   const htr_rect tile = toRect(u.tile), B = toRect(args.Fluid_bounds);
    ok(htr_diffusion_flux(d, &f, &tile, &B, taskStream()));
 }
 
@@ -179,12 +192,12 @@ void UpdateDucrosSensorTask::gpu_base_impl(const Args &args, Regions &regions,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 3);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 2, ctx, runtime);
    htr_fluid f = emptyFluid();
    f.velocity = u.ro<Vec3>(0, FID_velocity);
    for (int d = 0; d < 3; d++) { f.*DIR[d].nType = u.ro<int>(1, DIR[d].fNType); f.*DIR[d].m_d = u.ro<double>(1, DIR[d].fMd); }
    f.DucrosSensor = u.wo<double>(2, FID_DucrosSensor);
-   const htr_rect tile = toRect(u.domain(2)), B = toRect(args.Fluid_bounds);
+   const htr_rect tile = toRect(u.tile), B = toRect(args.Fluid_bounds);
    ok(htr_ducros_sensor(&f, &tile, &B, args.vorticityScale, taskStream()));
 }
 
@@ -193,14 +206,14 @@ void UpdateShockSensorTask<dir>::gpu_base_impl(const Args &args, Regions &region
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 3);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 2, ctx, runtime);
    const DirFields &D = DIR[dirIndex(dir)];
    htr_fluid f = emptyFluid();
    f.Conserved    = u.ro<VecNEq>(0, FID_Conserved);
    f.DucrosSensor = u.ro<double>(0, FID_DucrosSensor);
    f.*D.nType  = u.ro<int>(1, D.fNType);
    f.*D.sensor = u.wo<bool>(2, D.fSensor);
-   const htr_rect tile = toRect(u.domain(2)), B = toRect(args.Fluid_bounds);
+   const htr_rect tile = toRect(u.tile), B = toRect(args.Fluid_bounds);
    ok(htr_shock_sensor(dirIndex(dir), &f, &tile, &B, taskStream()));
 }
 
@@ -209,27 +222,27 @@ void AddChemistrySourcesTask::gpu_base_impl(const Args &args, Regions &regions,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 2);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 1, ctx, runtime);
    htr_fluid f = emptyFluid();
    f.rho = u.ro<double>(0, FID_rho); f.pressure = u.ro<double>(0, FID_pressure);
    f.temperature = u.ro<double>(0, FID_temperature); f.MassFracs = u.ro<VecNSp>(0, FID_MassFracs);
    f.Conserved_t = u.rw<VecNEq>(1, FID_Conserved_t);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(1));
+   const htr_rect tile = toRect(u.tile);
    ok(htr_add_chemistry_sources(&f, &tile, taskStream()));
 }
 
 void UpdateChemistryTask::gpu_base_impl(const Args &args, Regions &regions,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 2);
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 1, ctx, runtime);
    htr_fluid f = emptyFluid();
    f.Conserved_t     = u.ro<VecNEq>(0, FID_Conserved_t);
    f.Conserved       = u.rw<VecNEq>(1, FID_Conserved);
    f.Conserved_t_old = u.rw<VecNEq>(1, FID_Conserved_t_old);
    f.temperature     = u.rw<double>(1, FID_temperature);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(1));
+   const htr_rect tile = toRect(u.tile);
    ok(htr_update_chemistry(&f, &tile, futures[0].get_result<double>(), taskStream()));
 }
 
@@ -238,14 +251,14 @@ void UpdatePropertiesFromPrimitiveTask::gpu_base_impl(const Args &args, Regions 
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 2);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 1, ctx, runtime);
    htr_fluid f = emptyFluid();
    f.pressure = u.ro<double>(0, FID_pressure); f.temperature = u.ro<double>(0, FID_temperature);
    f.MolarFracs = u.ro<VecNSp>(0, FID_MolarFracs); f.velocity = u.ro<Vec3>(0, FID_velocity);
    f.MassFracs = u.wo<VecNSp>(1, FID_MassFracs); f.rho = u.wo<double>(1, FID_rho); f.mu = u.wo<double>(1, FID_mu);
    f.lam = u.wo<double>(1, FID_lam); f.Di = u.wo<VecNSp>(1, FID_Di); f.SoS = u.wo<double>(1, FID_SoS);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(1));
+   const htr_rect tile = toRect(u.tile);
    ok(htr_update_properties_from_primitive(&f, &tile, taskStream()));
 }
 
@@ -253,25 +266,49 @@ void UpdatePrimitiveFromConservedTask::gpu_base_impl(const Args &args, Regions &
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 2);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 1, ctx, runtime);
    htr_fluid f = emptyFluid();
    f.Conserved = u.ro<VecNEq>(0, FID_Conserved);
    f.temperature = u.rw<double>(1, FID_temperature); f.pressure = u.wo<double>(1, FID_pressure);
    f.MolarFracs = u.wo<VecNSp>(1, FID_MolarFracs); f.velocity = u.wo<Vec3>(1, FID_velocity);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(1));
+   const htr_rect tile = toRect(u.tile);
    ok(htr_update_primitive_from_conserved(&f, &tile, taskStream()));
 }
-// UpdateConservedFromPrimitiveTask iterates the rectangles of a sparse BC domain
-// (src/prometeo_variables.cu:184): it stays with the reference's body and calls
-// htr_update_conserved_from_primitive once per rectangle when ported.
+// The launch domain of UpdateConservedFromPrimitive is a union of rectangles (boundary-condition cells,
+// src/prometeo_variables.cc:113-131, src/prometeo_variables.cu:184): one call per rectangle, each addressed on its own.
+void UpdateConservedFromPrimitiveTask::gpu_base_impl(const Args &args, Regions &regions,
+                      const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 2);
+   (void)futures;
+   loadMix(args.mix);
+   const AccessorRO<VecNSp, 3> aY(regions[0], FID_MassFracs);
+   const AccessorRO<double, 3> aT(regions[0], FID_temperature);
+   const AccessorRO<  Vec3, 3> aU(regions[0], FID_velocity);
+   const AccessorRO<double, 3> aR(regions[0], FID_rho);
+   const AccessorWO<VecNEq, 3> aC(regions[1], FID_Conserved);
+   const Domain dom = runtime->get_index_space_domain(ctx, regions[1].get_logical_region().get_index_space());
+   for (RectInDomainIterator<3> Rit(dom); Rit(); Rit++) {
+      const Rect<3> r = *Rit;
+      htr_fluid f = emptyFluid();
+      size_t s[3];
+      #define HTR_PIECE(dst, acc, FT) { FT *p = (FT*)acc.ptr(r, s); \
+         for (int i = 0; i < 3; i++) f.dst.stride[i] = (int64_t)(s[i]*sizeof(FT)); \
+         f.dst.base = (char*)p - (r.lo.x*f.dst.stride[0] + r.lo.y*f.dst.stride[1] + r.lo.z*f.dst.stride[2]); }
+      HTR_PIECE(MassFracs, aY, VecNSp) HTR_PIECE(temperature, aT, double) HTR_PIECE(velocity, aU, Vec3)
+      HTR_PIECE(rho, aR, double) HTR_PIECE(Conserved, aC, VecNEq)
+      #undef HTR_PIECE
+      const htr_rect tile = toRect(r);
+      ok(htr_update_conserved_from_primitive(&f, &tile, taskStream()));
+   }
+}
 
 // ---- CFL -----------------------------------------------------------------------------------------
 DeferredValue<double> CalculateMaxSpectralRadiusTask::gpu_base_impl(const Args &args, Regions &regions,
                       const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
    assert(regions.size() == 1);
    (void)futures;
-   const Unpacker u = {regions, ctx, runtime};
+   const Unpacker u(regions, 0, ctx, runtime);
    htr_fluid f = emptyFluid();
    f.dcsi_d = u.ro<double>(0, FID_dcsi_d); f.deta_d = u.ro<double>(0, FID_deta_d); f.dzet_d = u.ro<double>(0, FID_dzet_d);
    f.MassFracs = u.ro<VecNSp>(0, FID_MassFracs); f.temperature = u.ro<double>(0, FID_temperature);
@@ -279,7 +316,7 @@ DeferredValue<double> CalculateMaxSpectralRadiusTask::gpu_base_impl(const Args &
    f.rho = u.ro<double>(0, FID_rho); f.mu = u.ro<double>(0, FID_mu); f.lam = u.ro<double>(0, FID_lam);
    f.Di = u.ro<VecNSp>(0, FID_Di); f.SoS = u.ro<double>(0, FID_SoS);
    loadMix(args.mix);
-   const htr_rect tile = toRect(u.domain(0));
+   const htr_rect tile = toRect(u.tile);
    DeferredValue<double> r(0.0);
    ok(htr_max_spectral_radius(&f, &tile, r.ptr(), taskStream()));
    return r;

@@ -101,6 +101,11 @@ int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double Integr
 /* Cells whose implicit integration hit the step/iteration caps since the last call (the reference
  * asserts there, src/Utils/math_utils.hpp:233,240).  Synchronises the device and resets the counter. */
 int htr_chemistry_failures(void);
+/* the same after synchronising `stream`, the stream the update was launched on (any kind of stream) */
+int htr_chemistry_failures_on(void *stream);
+/* 1 if htr_set_mixture has been called on the CURRENT device (all library state is per device: one process may drive
+ * several GPUs, src/prometeo_mapper.cc:231-262) */
+int htr_mixture_loaded(void);
 
 /* fp64 pipe probe (measurement only): runs independent DFMA chains for about `seconds` on the current device and
  * returns the sustained (tflops[0], last batch) and burst (tflops[1], best batch) DFMA rate in TFLOP/s: the

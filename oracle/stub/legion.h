@@ -23,6 +23,11 @@ enum legion_privilege_mode_stub { READ_ONLY = 1, READ_WRITE = 7, WRITE_ONLY = 0x
 
 namespace Realm {
    template<typename FT, int N, typename T> struct AffineAccessor {};
+   namespace Cuda {
+      // realm/cuda/cuda_access.h: the stream of the running GPU task (used when the CUDA runtime hijack is off)
+      inline void *&stub_task_stream() { static void *s = 0; return s; }
+      inline void *get_task_cuda_stream() { return stub_task_stream(); }
+   }
 }
 
 namespace Legion {
@@ -59,6 +64,7 @@ namespace Legion {
 
    struct Domain {
       Rect<3> r3; Rect<1> r1; bool dense;
+      std::vector<Rect<3> > pieces;
       Domain() : dense(true) {}
       Domain(const Rect<3> &r, bool d = true) : r3(r), dense(d) {}
       operator Rect<3>() const {
@@ -71,7 +77,12 @@ namespace Legion {
    // An index space is a bounding rectangle plus a flag: the reference's ghost partitions are unions of shifted /
    // wrapped pieces (src/prometeo_partitioner.rg:1239+), i.e. SPARSE -- converting such a domain to a Rect aborts in
    // Legion, and so it does here (tests/test_adapter_gpu.py drives the adapter with sparse ghost regions).
-   struct IndexSpace { Rect<3> bounds; bool dense; IndexSpace() : dense(true) {} IndexSpace(const Rect<3> &b, bool d = true) : bounds(b), dense(d) {} };
+   struct IndexSpace {
+      Rect<3> bounds; bool dense;
+      std::vector<Rect<3> > pieces;          // the rectangles of a sparse space (RectInDomainIterator walks them)
+      IndexSpace() : dense(true) {}
+      IndexSpace(const Rect<3> &b, bool d = true) : bounds(b), dense(d) {}
+   };
    struct FieldSpace { unsigned id; };
    struct LogicalRegion {
       unsigned tree_id; unsigned long long index_space_id; unsigned is_tid; unsigned type_tag; unsigned field_space_id;
@@ -114,7 +125,7 @@ namespace Legion {
       void set_leaf(bool = true) {}
    };
    struct Runtime {
-      Domain get_index_space_domain(Context, const IndexSpace &is) { return Domain(is.bounds, is.dense); }
+      Domain get_index_space_domain(Context, const IndexSpace &is) { Domain d(is.bounds, is.dense); d.pieces = is.pieces; return d; }
       template<void (*F)(const Task*, const std::vector<PhysicalRegion>&, Context, Runtime*)>
       static void preregister_task_variant(const TaskVariantRegistrar&, const char*) {}
       template<typename R, R (*F)(const Task*, const std::vector<PhysicalRegion>&, Context, Runtime*)>
@@ -130,7 +141,13 @@ namespace Legion {
       T* ptr() { return p ? p : &v; }
    };
    template<typename T, int N> struct DeferredBuffer {};
-   template<int N> struct RectInDomainIterator {};
+   template<int N> struct RectInDomainIterator {
+      std::vector<Rect<3> > rects; size_t k;
+      RectInDomainIterator(const Domain &d) : rects(d.pieces), k(0) { if (rects.empty()) rects.push_back(d.r3); }
+      bool operator()() const { return k < rects.size(); }
+      const Rect<3>& operator*() const { return rects[k]; }
+      RectInDomainIterator& operator++(int) { k++; return *this; }
+   };
 
    // Accessor over a raw strided host array (byte strides, like Realm::AffineAccessor).
    template<int PRIV, typename FT, int N, typename T = coord_t, typename A = Realm::AffineAccessor<FT, N, T> >

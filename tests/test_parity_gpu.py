@@ -281,9 +281,10 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
     fl = to_device(s, f)
     out = {}
     try:
-        # 1: the two-pass z-marching kernels (csrc/htr_march.cuh, the default); 2: the four staged kernels of
-        # csrc/htr_fast.cuh ("march" = 0); 0: the per-task kernels ("fast" = 0)
-        for path, (fast, march) in {1: (1, 1), 2: (1, 0), 0: (0, 0)}.items():
+        # 1: the two-pass z-marching kernels (csrc/htr_march.cuh, "march" = 3); 2: the four staged kernels of
+        # csrc/htr_fast.cuh ("march" = 0); 3: the default (Euler-z march + three staged kernels); 0: the per-task kernels
+        # 4: Euler-z march + plane march without its diffusion phase + staged diffusion ("march" = 5)
+        for path, (fast, march) in {1: (1, 3), 2: (1, 0), 3: (1, 1), 4: (1, 5), 0: (0, 0)}.items():
             s.set_option("fast", fast)
             s.set_option("march", march)
             fl.t["Conserved_t"].fill_(-3.0)
@@ -301,11 +302,11 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
         f["Conserved_t"][...] = ref
     if variant == "strict":
-        assert np.array_equal(out[1], out[0])
-        assert np.array_equal(out[2], out[0])
+        for k in (1, 2, 3, 4):
+            assert np.array_equal(out[k], out[0]), k
     else:
-        assert scaled_err(out[1], out[0], scale) <= TOL_FLUX
-        assert scaled_err(out[2], out[0], scale) <= TOL_FLUX
+        for k in (1, 2, 3, 4):
+            assert scaled_err(out[k], out[0], scale) <= TOL_FLUX, k
     assert scaled_err(out[1], f["Conserved_t"], scale) <= (TOL_CHEM if chem else TOL_FLUX)
 
 
@@ -326,14 +327,14 @@ def test_march_rhs_equals_per_task_sequence(cfg, chem, kw, diffusion, kz, kp):
     fl = to_device(s, f)
     out = {}
     try:
-        s.set_option("march_kz", kz); s.set_option("march_kp", kp)
+        s.set_option("march_kz", kz); s.set_option("march_kp", kp); s.set_option("march", 3)
         for fast in (1, 0):
             s.set_option("fast", fast)
             fl.t["Conserved_t"].fill_(-3.0)
             s.UpdateDerivatives(fl, "Hybrid", diffusion=diffusion, chemistry=chem, RK_coeffs=(0.75, 0.25), deltaTime=1e-3)
             out[fast] = fl.download(["Conserved_t"])["Conserved_t"]
     finally:
-        s.set_option("fast", 1); s.set_option("march_kz", 64); s.set_option("march_kp", 32)
+        s.set_option("fast", 1); s.set_option("march_kz", 64); s.set_option("march_kp", 32); s.set_option("march", 1)
     assert np.isfinite(out[1]).all()
     bad = np.argwhere(out[1] != out[0])
     assert bad.size == 0, (len(bad), bad[:5].tolist())
