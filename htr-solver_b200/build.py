@@ -6,7 +6,7 @@ import argparse, os, subprocess, sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-MIXES = ["ConstPropMix", "AirMix"]
+MIXES = ["ConstPropMix", "AirMix", "CH41StMix"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-shared", "--expt-relaxed-constexpr",

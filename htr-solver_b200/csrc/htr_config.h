@@ -18,8 +18,20 @@
 #  define HTR_MAX_REACTANTS 2
 #  define HTR_MAX_PRODUCTS 2
 #  define HTR_MAX_TB 5
+#elif defined(HTR_MIX_CH41StMix)
+   // src/Mixtures/CH41StMix.hpp:34-53: one-step methane oxidation with specified forward orders (FWD_ORDERS)
+#  define HTR_MIX_NAME "CH41StMix"
+#  define HTR_NSPEC 4
+#  define HTR_MULTICOMP 1
+#  define HTR_NREAC 1
+#  define HTR_NTBREAC 0
+#  define HTR_NFOREAC 0
+#  define HTR_MAX_REACTANTS 2
+#  define HTR_MAX_PRODUCTS 2
+#  define HTR_MAX_TB 0
+#  define HTR_FWD_ORDERS 1
 #else
-#  error "define HTR_MIX_<Mixture> (ConstPropMix | AirMix)"
+#  error "define HTR_MIX_<Mixture> (ConstPropMix | AirMix | CH41StMix)"
 #endif
 
 #define HTR_NEQ (HTR_NSPEC + 4)

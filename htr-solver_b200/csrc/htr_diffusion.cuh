@@ -1,3 +1,39 @@
+// ---------------------------------------------------------------------------------------------------------------
+// ATTRIBUTION.  The kernel structure of this file is original, but parts of its arithmetic restate, expression for
+// expression (bit parity with the reference requires it), formulas of the HTR solver (stanfordhpccenter/HTR-solver,
+// src/prometeo_rhs.inl, prometeo_metric.inl, prometeo_sensor.inl, prometeo_variables.hpp, prometeo_cfl.hpp, Mixtures/*,
+// Utils/math_utils.hpp; the file:line citations below say which).  That code is distributed under the following notice,
+// retained here as its conditions require:
+//
+// Copyright (c) "2019, by Stanford University
+//               Developer: Mario Di Renzo
+//               Affiliation: Center for Turbulence Research, Stanford University
+//               URL: https://ctr.stanford.edu
+//               Citation: Di Renzo, M., Lin, F., and Urzay, J. (2020).
+//                         HTR solver: An open-source exascale-oriented task-based
+//                         multi-GPU high-order code for hypersonic aerothermodynamics.
+//                         Computer Physics Communications 255, 107262"
+// All rights reserved.
+//
+// Redistribution and use in source and binary forms, with or without
+// modification, are permitted provided that the following conditions are met:
+//    * Redistributions of source code must retain the above copyright
+//      notice, this list of conditions and the following disclaimer.
+//    * Redistributions in binary form must reproduce the above copyright
+//      notice, this list of conditions and the following disclaimer in the
+//      documentation and/or other materials provided with the distribution.
+//
+// THIS SOFTWARE IS PROVIDED BY THE COPYRIGHT HOLDERS AND CONTRIBUTORS "AS IS" AND
+// ANY EXPRESS OR IMPLIED WARRANTIES, INCLUDING, BUT NOT LIMITED TO, THE IMPLIED
+// WARRANTIES OF MERCHANTABILITY AND FITNESS FOR A PARTICULAR PURPOSE ARE
+// DISCLAIMED. IN NO EVENT SHALL THE COPYRIGHT HOLDER BE LIABLE FOR ANY
+// DIRECT, INDIRECT, INCIDENTAL, SPECIAL, EXEMPLARY, OR CONSEQUENTIAL DAMAGES
+// (INCLUDING, BUT NOT LIMITED TO, PROCUREMENT OF SUBSTITUTE GOODS OR SERVICES;
+// LOSS OF USE, DATA, OR PROFITS; OR BUSINESS INTERRUPTION) HOWEVER CAUSED AND
+// ON ANY THEORY OF LIABILITY, WHETHER IN CONTRACT, STRICT LIABILITY, OR TORT
+// (INCLUDING NEGLIGENCE OR OTHERWISE) ARISING IN ANY WAY OUT OF THE USE OF THIS
+// SOFTWARE, EVEN IF ADVISED OF THE POSSIBILITY OF SUCH DAMAGE.
+// ---------------------------------------------------------------------------------------------------------------
 // Diffusion face flux at i+1/2 along `dir` (viscous stress, Fourier + species-enthalpy heat
 // flux, Fickian species flux with correction velocity), 2nd-order staggered.
 // Arithmetic of src/prometeo_rhs.inl:1058-1215 (GetSigma, GetDiffusionFlux); each face is

@@ -760,6 +760,10 @@ using namespace htr;
 #include "generated/AirMix_tables.inc"
 #define HTR_TABLES htr_AirMix_tables
 #define HTR_TABLE_BYTES HTR_AIRMIX_TABLE_BYTES
+#elif defined(HTR_MIX_CH41StMix)
+#include "generated/CH41StMix_tables.inc"
+#define HTR_TABLES htr_CH41StMix_tables
+#define HTR_TABLE_BYTES HTR_CH41STMIX_TABLE_BYTES
 #endif
 #endif
 
@@ -924,6 +928,14 @@ int htr_set_mixture(const void *mix, size_t bytes) {
          for (int i = 0; i < n; i++) if (x[i].ind != y[i].ind || x[i].nu != y[i].nu) return false;
          return true;
       };
+#ifdef HTR_FWD_ORDERS
+      auto sameReact = [](const ReactTerm *x, const ReactTerm *y, int n) {
+         for (int i = 0; i < n; i++) if (x[i].ind != y[i].ind || x[i].nu != y[i].nu || x[i].ord != y[i].ord) return false;
+         return true;
+      };
+#else
+      auto sameReact = sameTerms;
+#endif
       auto sameK = [](const Arrhenius &x, const Arrhenius &y) {
          return (x.n != 0.0f) == (y.n != 0.0f) && (fabsf(x.EovR) > 1e-5f) == (fabsf(y.EovR) > 1e-5f);
       };
@@ -931,14 +943,14 @@ int htr_set_mixture(const void *mix, size_t bytes) {
       for (int r = 0; r < HTR_NREAC; r++) {
          const PlainReaction &x = a.reactions[r], &y = b.reactions[r];
          if (x.has_backward != y.has_backward || x.Neducts != y.Neducts || x.Npducts != y.Npducts || !sameK(x.k, y.k) ||
-             !sameTerms(x.educts, y.educts, y.Neducts) || !sameTerms(x.pducts, y.pducts, y.Npducts)) return HTR_EMIXTYPE;
+             !sameReact(x.educts, y.educts, y.Neducts) || !sameTerms(x.pducts, y.pducts, y.Npducts)) return HTR_EMIXTYPE;
       }
 #endif
 #if HTR_NTBREAC > 0
       for (int r = 0; r < HTR_NTBREAC; r++) {
          const CollisionReaction &x = a.tbReactions[r], &y = b.tbReactions[r];
          if (x.has_backward != y.has_backward || x.Neducts != y.Neducts || x.Npducts != y.Npducts || x.Nthirdb != y.Nthirdb ||
-             !sameK(x.k, y.k) || !sameTerms(x.educts, y.educts, y.Neducts) || !sameTerms(x.pducts, y.pducts, y.Npducts) ||
+             !sameK(x.k, y.k) || !sameReact(x.educts, y.educts, y.Neducts) || !sameTerms(x.pducts, y.pducts, y.Npducts) ||
              !sameTerms(x.thirdb, y.thirdb, y.Nthirdb)) return HTR_EMIXTYPE;
       }
 #endif

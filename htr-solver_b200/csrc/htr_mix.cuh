@@ -1,3 +1,39 @@
+// ---------------------------------------------------------------------------------------------------------------
+// ATTRIBUTION.  The kernel structure of this file is original, but parts of its arithmetic restate, expression for
+// expression (bit parity with the reference requires it), formulas of the HTR solver (stanfordhpccenter/HTR-solver,
+// src/prometeo_rhs.inl, prometeo_metric.inl, prometeo_sensor.inl, prometeo_variables.hpp, prometeo_cfl.hpp, Mixtures/*,
+// Utils/math_utils.hpp; the file:line citations below say which).  That code is distributed under the following notice,
+// retained here as its conditions require:
+//
+// Copyright (c) "2019, by Stanford University
+//               Developer: Mario Di Renzo
+//               Affiliation: Center for Turbulence Research, Stanford University
+//               URL: https://ctr.stanford.edu
+//               Citation: Di Renzo, M., Lin, F., and Urzay, J. (2020).
+//                         HTR solver: An open-source exascale-oriented task-based
+//                         multi-GPU high-order code for hypersonic aerothermodynamics.
+//                         Computer Physics Communications 255, 107262"
+// All rights reserved.
+//
+// Redistribution and use in source and binary forms, with or without
+// modification, are permitted provided that the following conditions are met:
+//    * Redistributions of source code must retain the above copyright
+//      notice, this list of conditions and the following disclaimer.
+//    * Redistributions in binary form must reproduce the above copyright
+//      notice, this list of conditions and the following disclaimer in the
+//      documentation and/or other materials provided with the distribution.
+//
+// THIS SOFTWARE IS PROVIDED BY THE COPYRIGHT HOLDERS AND CONTRIBUTORS "AS IS" AND
+// ANY EXPRESS OR IMPLIED WARRANTIES, INCLUDING, BUT NOT LIMITED TO, THE IMPLIED
+// WARRANTIES OF MERCHANTABILITY AND FITNESS FOR A PARTICULAR PURPOSE ARE
+// DISCLAIMED. IN NO EVENT SHALL THE COPYRIGHT HOLDER BE LIABLE FOR ANY
+// DIRECT, INDIRECT, INCIDENTAL, SPECIAL, EXEMPLARY, OR CONSEQUENTIAL DAMAGES
+// (INCLUDING, BUT NOT LIMITED TO, PROCUREMENT OF SUBSTITUTE GOODS OR SERVICES;
+// LOSS OF USE, DATA, OR PROFITS; OR BUSINESS INTERRUPTION) HOWEVER CAUSED AND
+// ON ANY THEORY OF LIABILITY, WHETHER IN CONTRACT, STRICT LIABILITY, OR TORT
+// (INCLUDING NEGLIGENCE OR OTHERWISE) ARISING IN ANY WAY OUT OF THE USE OF THIS
+// SOFTWARE, EVEN IF ADVISED OF THE POSSIBILITY OF SUCH DAMAGE.
+// ---------------------------------------------------------------------------------------------------------------
 // Mixture thermodynamics, transport and kinetics evaluated in registers from the parameter
 // block in __constant__ memory.  Free functions over plain arrays; one set per mixture family.
 //
@@ -442,6 +478,18 @@ HTR_DEV double massAction(const StoichTerm *t, int n, const double *C) {
    }
    return a;
 }
+#ifdef HTR_FWD_ORDERS
+// forward rate with specified reaction orders (src/Mixtures/Reaction.inl:110-124 under FWD_ORDERS)
+HTR_DEV double massAction(const ReactTerm *t, int n, const double *C) {
+   double a = 1.0;
+   for (int i = 0; i < n; i++) {
+      const int ind = t[i].ind;
+      if (t[i].ord == 1) a *= C[ind];
+      else               a *= pow(C[ind], (double)t[i].ord);
+   }
+   return a;
+}
+#endif
 template<class R>
 HTR_DEV double backwardRateCoeff(const R &r, double Kf, double P, double T, const double *G) {
    double sumNu = 0.0, sumNuG = 0.0;
@@ -475,12 +523,14 @@ HTR_DEV void scatter(const R &r, double rate, double *w) {
 //   * the structure of the mechanism (species indices, stoichiometric coefficients, which Arrhenius terms
 //     exist) is compile-time (generated/<Mix>_mechanism.inc), so every array index is a literal after
 //     unrolling: no local memory, no select chains; nu = 2 is a multiplication.
-HTR_DEV double powNu(double c, float nu) { return (nu == 1.0f) ? c : ((nu == 2.0f) ? c*c : pow(c, (double)nu)); }
+HTR_DEV double powNu(double c, float nu) { return (nu == 1.0f) ? c : ((nu == 2.0f) ? c*c : ((nu == 0.5f) ? sqrt(c) : pow(c, (double)nu))); }
 HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, const double *Yi) {
    // structure of the mechanism as compile-time tables (generated/<Mix>_mechanism.inc); htr_set_mixture
    // refuses a mixture block whose reaction tables differ from the ones these were generated from
 #if defined(HTR_MIX_AirMix)
 #include "generated/AirMix_mechanism.inc"
+#elif defined(HTR_MIX_CH41StMix)
+#include "generated/CH41StMix_mechanism.inc"
 #endif
    static_assert(MECH_NR == HTR_NREAC + HTR_NTBREAC, "mechanism tables out of date");
    const double T = Tn*c_mix.TRef;
@@ -498,14 +548,18 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
    const double cM = P/(RGAS*T);
    HTR_UNROLL
    for (int r = 0; r < MECH_NR; r++) {
+#if HTR_NTBREAC > 0
       const Arrhenius k = (r < HTR_NREAC) ? c_mix.reactions[r < HTR_NREAC ? r : 0].k
                                           : c_mix.tbReactions[r >= HTR_NREAC ? r - HTR_NREAC : 0].k;
+#else
+      const Arrhenius k = c_mix.reactions[r].k;
+#endif
       double ex = 0.0;
       if (MECH_HASN[r]) ex += k.n*logT;
       if (MECH_HASE[r]) ex -= k.EovR*iT;
       double a = 1.0;
       HTR_UNROLL
-      for (int i = 0; i < HTR_MAX_REACTANTS; i++) if (i < MECH_NE[r]) a *= powNu(C[MECH_EI[r][i]], MECH_EN[r][i]);
+      for (int i = 0; i < HTR_MAX_REACTANTS; i++) if (i < MECH_NE[r]) a *= powNu(C[MECH_EI[r][i]], MECH_EO[r][i]);   // EO = EN unless FWD_ORDERS
       double rate = k.A*exp(ex)*a;
       if (MECH_BW[r]) {
          double sumNu = 0.0, sumNuG = 0.0, b = 1.0;
@@ -521,7 +575,7 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
       if (r >= HTR_NREAC && MECH_NT[r] > 0) {
          double c = cM;
          HTR_UNROLL
-         for (int i = 0; i < HTR_MAX_TB; i++) if (i < MECH_NT[r]) c += C[MECH_TI[r][i]]*(MECH_TN[r][i] - 1.0);
+         for (int i = 0; i < (HTR_MAX_TB > 0 ? HTR_MAX_TB : 1); i++) if (i < MECH_NT[r]) c += C[MECH_TI[r][i]]*(MECH_TN[r][i] - 1.0);
          rate *= c;
       }
       HTR_UNROLL

@@ -41,22 +41,27 @@ struct SpeciesData {
 };
 static_assert(sizeof(SpeciesData) == 312, "species layout");
 
-struct StoichTerm { uint8_t ind; float nu; };     // reactant, product (nu) or collider (efficiency)
+struct StoichTerm { uint8_t ind; float nu; };     // product (nu) or collider (efficiency)
+#ifdef HTR_FWD_ORDERS
+struct ReactTerm { uint8_t ind; float nu; float ord; };    // reactant with its specified order (src/Mixtures/Reaction.hpp:100-107)
+#else
+typedef StoichTerm ReactTerm;
+#endif
 struct Arrhenius  { double A; float n; float EovR; };
 struct PlainReaction {
    Arrhenius k;
    bool    has_backward;
    uint8_t Neducts, Npducts;
-   StoichTerm educts[HTR_MAX_REACTANTS];
+   ReactTerm  educts[HTR_MAX_REACTANTS];
    StoichTerm pducts[HTR_MAX_PRODUCTS];
 };
 struct CollisionReaction {
    Arrhenius k;
    bool    has_backward;
    uint8_t Neducts, Npducts, Nthirdb;
-   StoichTerm educts[HTR_MAX_REACTANTS];
+   ReactTerm  educts[HTR_MAX_REACTANTS];
    StoichTerm pducts[HTR_MAX_PRODUCTS];
-   StoichTerm thirdb[HTR_MAX_TB];
+   StoichTerm thirdb[HTR_MAX_TB > 0 ? HTR_MAX_TB : 1];
 };
 
 struct MixData {

@@ -17,6 +17,10 @@ CONSTPROP_VISCOUS = {"type": "ConstPropMix", "gasConstant": 1.0, "gamma": 1.4, "
 AIRMIX_3DPERIODIC = {"type": "AirMix", "LRef": 1.0, "TRef": 500.0, "PRef": 100000.0,
                      "XiRef": {"Species": [{"Name": "N2", "MolarFrac": 0.79}, {"Name": "O2", "MolarFrac": 0.21}]}}  # solverTests/3DPeriodic_Air/base.json
 AIR_SPECIES = ["N2", "O2", "NO", "N", "O"]
+# one-step methane oxidation (src/Mixtures/CH41StMix.hpp); reference state as in unitTests/mixTest/CH41StMix.json
+CH41ST_3DPERIODIC = {"type": "CH41StMix", "LRef": 1.0, "TRef": 300.0, "PRef": 101325.0,
+                     "XiRef": {"Species": [{"Name": "O2", "MolarFrac": 1.0}]}}
+SPECIES = {"AirMix": AIR_SPECIES, "CH41StMix": ["CH4", "O2", "CO2", "H2O"]}
 
 
 def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=0.0, species_wave=0.0,
@@ -31,7 +35,8 @@ def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=
     nx, ny, nz = (n, n, n) if np.isscalar(n) else n
     gx, gy, gz = (nx, ny, nz) if global_n is None else ((global_n,) * 3 if np.isscalar(global_n) else global_n)
     multi = mix_cfg["type"] != "ConstPropMix"
-    nspec = 5 if multi else 1
+    names = SPECIES.get(mix_cfg["type"], ["MIX"])
+    nspec = len(names)
     if p0 is None:
         p0, T0, U = (1.0, 1.0, 0.002634364032587426) if multi else (100.0, 100.0, 1.0)
     # (nx,ny,nz) is this block of a (gx,gy,gz) global box, starting at cell `offset`;
@@ -62,15 +67,25 @@ def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=
     Xi = np.zeros((nz, ny, nx, nspec))
     if multi:
         ref = {s["Name"]: s["MolarFrac"] for s in mix_cfg["XiRef"]["Species"]}
-        for i, s in enumerate(AIR_SPECIES):
+        for i, s in enumerate(names):
             Xi[..., i] = ref.get(s, 1.0e-60)
-        if species_wave > 0.0:
+        if species_wave > 0.0 and mix_cfg["type"] == "AirMix":
             w = species_wave
             Xi[..., 1] += w * 0.05 * np.sin(X) * np.cos(2 * Y)
             Xi[..., 2] = w * 0.01 * (1.1 + np.sin(2 * X + Z))
             Xi[..., 3] = w * 0.002 * (1.1 + np.cos(Y + 2 * Z))
             Xi[..., 4] = w * 0.005 * (1.1 + np.sin(X + Y + Z))
             Xi[..., 0] = 1.0 - Xi[..., 1:].sum(axis=-1)
+        elif species_wave > 0.0:
+            # any other mixture: smooth waves on every species but the dominant one of the reference state
+            w = species_wave
+            dom = int(np.argmax([ref.get(s, 0.0) for s in names]))
+            k = 0
+            for i in range(nspec):
+                if i != dom:
+                    Xi[..., i] = w * (0.04 / (1 + k)) * (1.1 + np.sin((1 + k % 2) * X + (k // 2) * Y + Z + 0.7 * k))
+                    k += 1
+            Xi[..., dom] = 1.0 - (Xi.sum(axis=-1) - Xi[..., dom])
     else:
         Xi[..., 0] = 1.0
     f["pressure"] = np.ascontiguousarray(P, dtype=dtype)

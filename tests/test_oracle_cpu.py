@@ -39,7 +39,7 @@ def test_mixtest_airmix_goldens():
     assert abs(1.0 / np.sum(0.2 / W) - 2.135186e-02) / 2.135186e-02 < 1e-3
 
 
-@pytest.mark.parametrize("mix,cfg", [("AirMix", synthetic.AIRMIX_3DPERIODIC), ("AirMix", MIXTEST_AIR),
+@pytest.mark.parametrize("mix,cfg", [("AirMix", synthetic.AIRMIX_3DPERIODIC), ("AirMix", MIXTEST_AIR), ("CH41StMix", synthetic.CH41ST_3DPERIODIC),
                                      ("ConstPropMix", synthetic.CONSTPROP_VISCOUS), ("ConstPropMix", synthetic.CONSTPROP_3DPERIODIC)])
 def test_mixture_block_is_byte_identical(mix, cfg):
     if not have_oracle(mix):
@@ -56,7 +56,7 @@ def test_cabi_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "htr_b200.h")).read()
     names = sorted(set(re.findall(r"\b(htr_[a-z_0-9]+)\s*\(", hdr)))
     assert len(names) >= 20
-    for mix in ("ConstPropMix", "AirMix"):
+    for mix in ("ConstPropMix", "AirMix", "CH41StMix"):
         L = htr.load_library(mix)
         for n in names:
             assert hasattr(L, n), (mix, n)

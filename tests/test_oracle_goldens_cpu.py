@@ -193,3 +193,40 @@ def test_mathutils_goldens():
     y = np.array([1.0, 1.0, 0.0])
     o.lib.htr_oracle_rosenbrock3(y.ctypes.data, 1.0e-3, 25.0)
     assert np.all(np.abs(1.0 - y / np.array([7.818640e-01, 1.218133e+00, -2.655799e-06])) < 1e-6)
+
+
+@pytest.mark.skipif(not have_oracle("CH41StMix"), reason="oracle/_ref not built")
+def test_mixtest_ch41stmix_goldens():
+    """unitTests/mixTest/mixTest.rg:173-215 (CH41StMix: T = 750 K, P = 1 atm, Y_i = 0.25; reference state pure O2):
+    thermodynamics, transport and the one-step kinetics with specified forward orders, to the 7 printed digits."""
+    cfg = {"type": "CH41StMix", "LRef": 1.0, "PRef": 101325.0, "TRef": 300.0,
+           "XiRef": {"Species": [{"Name": "O2", "MolarFrac": 1.0}]}}
+    o = Oracle("CH41StMix"); o.init_mix(cfg)
+    P, T = 101325.0, 750.0
+    q = refs(101325.0, 300.0, 3.1998800000000e-02)
+    r = o.mix_eval(1.0, T / 300.0, [0.25] * 4)
+    tol = 1e-6
+    def chk(got, exp, what):
+        assert abs(got / exp - 1.0) < tol, (what, got, exp)
+    EMixW = 2.328035e-02
+    Erho = P * EMixW / (R * T)
+    W = np.array([o.lib.htr_oracle_species_W(i) for i in range(4)])
+    assert np.allclose(W, [16.04206e-03, 2 * 15.9994e-3, 44.00950e-03, 18.01508e-03], rtol=1e-7)
+    chk(1.0 / np.sum(0.25 / W), EMixW, "MixW")
+    for i, e in enumerate([3.628018e-01, 1.818846e-01, 1.322462e-01, 3.230675e-01]):
+        chk(r["Xi"][i], e, f"Xi[{i}]")
+    chk(r["rho"] * q["rhoRef"], Erho, "rho")
+    chk(r["cp"] * q["CpRef"], 2.032494e+03, "cp")
+    chk(r["h"] * q["eRef"], -5.965912e+06, "h")
+    chk(r["mu"] * q["muRef"], 3.108639e-05, "mu")
+    chk(r["lam"] * q["lamRef"], 8.767210e-02, "lam")
+    chk(r["gamma"], 1.213177e+00, "gamma")
+    chk(r["SoS"] * q["uRef"], 5.700526e+02, "SoS")
+    for i, e in enumerate([1.343289e-04, 1.007327e-04, 7.760974e-05, 1.350278e-04]):
+        chk(r["Di"][i] * q["DiRef"], e, f"Di[{i}]")
+    for i, e in enumerate([-2.658098e+00, -1.060412e+01, 7.292178e+00, 5.970037e+00]):
+        chk(r["w"][i] * q["wiRef"], e, f"w[{i}]")
+    for i, e in enumerate([-1.550405e+05, -1.186804e+06, 6.509754e+05, 1.762304e+06]):
+        chk(r["dpdrhoi"][i] * q["eRef"], e, f"dpdrhoi[{i}]")
+    for i, e in enumerate([-3.294307e+06, 4.425045e+05, -8.481094e+06, -1.253075e+07]):
+        chk(o.lib.htr_oracle_species_enthalpy(i, T / 300.0) * q["eRef"], e, f"hsp[{i}]")
