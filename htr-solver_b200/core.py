@@ -268,9 +268,19 @@ class Solver:
         t, _ = self._rects(fl, tile, None)
         self._check(self.L.htr_add_chemistry_sources(C.byref(fl.struct()), t, self._stream()), "htr_add_chemistry_sources")
 
-    def UpdateChemistry(self, fl, Integrator_deltaTime, tile=None):
+    def UpdateChemistry(self, fl, Integrator_deltaTime, tile=None, rhs_counts=None):
+        """rhs_counts: optional int32 CUDA tensor (one entry per cell of the tile) that receives the number of
+        right-hand-side evaluations of every cell (diagnostic of the adaptive step sequence)."""
         t, _ = self._rects(fl, tile, None)
-        self._check(self.L.htr_update_chemistry(C.byref(fl.struct()), t, Integrator_deltaTime, self._stream()), "htr_update_chemistry")
+        if rhs_counts is not None:
+            self.L.htr_chemistry_rhs_counts.argtypes = [C.c_void_p]
+            self._check(self.L.htr_chemistry_rhs_counts(C.c_void_p(rhs_counts.data_ptr())), "htr_chemistry_rhs_counts")
+        try:
+            self._check(self.L.htr_update_chemistry(C.byref(fl.struct()), t, Integrator_deltaTime, self._stream()), "htr_update_chemistry")
+        finally:
+            if rhs_counts is not None:
+                self.torch.cuda.current_stream().synchronize()
+                self.L.htr_chemistry_rhs_counts(C.c_void_p(0))
         nfail = self.L.htr_chemistry_failures_on(self._stream())
         if nfail:
             raise HTRError(f"implicit chemistry did not converge in {nfail} cells")

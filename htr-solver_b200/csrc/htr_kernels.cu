@@ -476,17 +476,20 @@ __global__ void __launch_bounds__(128) chem_source_kernel(const htr_fluid f, con
 
 __device__ int d_chem_failures;
 
-__global__ void __launch_bounds__(64) update_chemistry_kernel(const htr_fluid f, const htr_rect tile, const double dt) {
+__device__ int *d_chem_calls;      // optional diagnostic output (htr_chemistry_rhs_counts): rhs() evaluations per cell of the tile
+
+__global__ void __launch_bounds__(128) update_chemistry_kernel(const htr_fluid f, const htr_rect tile, const double dt) {
    Pt p; if (!cellOf(p, tile)) return;
    double S[nEq], x[nEq];
    const double *Ct = at<const double>(f.Conserved_t, p);
    double *Cto = at<double>(f.Conserved_t_old, p);
    double *C = at<double>(f.Conserved, p);
    for (int i = 0; i < nEq; i++) { S[i] = Ct[i]; Cto[i] = S[i]; x[i] = C[i]; }
-   ChemProblem prob; prob.S = S; prob.T = *at<double>(f.temperature, p);
+   ChemProblem prob; prob.S = S; prob.T = *at<double>(f.temperature, p); prob.calls = 0;
    if (!rosenbrockSolve<nEq>(prob, x, dt, dt)) atomicAdd(&d_chem_failures, 1);
    for (int i = 0; i < nEq; i++) C[i] = x[i];
    *at<double>(f.temperature, p) = prob.T;
+   if (d_chem_calls) d_chem_calls[maskIndexG(p, tile)] = prob.calls;
 }
 
 // NEWTON = false: the temperature field already holds the converged value of these cells (ghost copies of a
@@ -1070,13 +1073,19 @@ int htr_add_chemistry_sources(const htr_fluid *f, const htr_rect *tile, void *st
 
 int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double dt, void *stream) {
    HTR_CHECK_COMMON(f, tile)
-   update_chemistry_kernel<<<blocksFor(*tile, 64), 64, 0, (cudaStream_t)stream>>>(*f, *tile, dt);
+   update_chemistry_kernel<<<blocksFor(*tile, 128), 128, 0, (cudaStream_t)stream>>>(*f, *tile, dt);
    return cuerr(cudaGetLastError());
 }
 
 /* number of cells whose implicit integration hit the iteration caps since the last call
  * (the reference asserts, src/Utils/math_utils.hpp:233,240); synchronises the device */
 int htr_chemistry_failures(void);
+/* diagnostic: subsequent htr_update_chemistry calls write the number of rhs() evaluations of every cell of their tile
+ * (dense, x fastest) to the DEVICE buffer `d_counts`; NULL switches it off.  (2 nEq + 1) evaluations per integration step
+ * plus 3 per attempt: equal counts = same adaptive step sequence as the reference (oracle: ..._counted). */
+int htr_chemistry_rhs_counts(int *d_counts) {
+   return cuerr(cudaMemcpyToSymbol(d_chem_calls, &d_counts, sizeof(int*)));
+}
 int htr_mixture_loaded(void) { return g_mix_loaded ? 1 : 0; }
 
 /* the same, ordered after the work queued on `stream` (cudaMemcpyFromSymbol alone only orders against the legacy default

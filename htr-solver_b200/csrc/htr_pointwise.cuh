@@ -104,19 +104,26 @@ HTR_DEV void primitivesFromConserved(const double *U, double &rho, double *Yi, d
 }
 
 // ---- chemistry -----------------------------------------------------------------------------
-struct ChemProblem {            // dU/dt = w(U) + S, S frozen (the explicit RHS of the other terms)
+// One evaluation of dU/dt = w(U) + S (S frozen: the explicit RHS of the other terms).  Deliberately NOT inlined: the
+// integrator calls it from 2 nEq + 4 places per step; inlined and unrolled that was 30 000 SASS instructions (480 KB,
+// far beyond the instruction cache: `no_instruction` was the top stall of update_chemistry_kernel, profiles/r2_*).
+__device__ __noinline__ void chemRhs(double *r, const double *x, const double *S, double *T) {
+   double rho, Yi[nSpec], MixW, u[3], P;
+   double Tl = *T;
+   primitivesFromConserved(x, rho, Yi, MixW, u, Tl, P);
+   *T = Tl;
+   double w[nSpec];
+   mix::GetProductionRates(w, rho, P, Tl, Yi);
+   HTR_UNROLL
+   for (int i = 0; i < nSpec; i++) r[i] = w[i] + S[i];
+   HTR_UNROLL
+   for (int i = nSpec; i < nEq; i++) r[i] = S[i];
+}
+struct ChemProblem {
    const double *S;
    double T;                    // running Newton guess, updated by every evaluation
-   __device__ void rhs(double *r, const double *x) {
-      double rho, Yi[nSpec], MixW, u[3], P;
-      primitivesFromConserved(x, rho, Yi, MixW, u, T, P);
-      double w[nSpec];
-      mix::GetProductionRates(w, rho, P, T, Yi);
-      HTR_UNROLL
-      for (int i = 0; i < nSpec; i++) r[i] = w[i] + S[i];
-      HTR_UNROLL
-      for (int i = nSpec; i < nEq; i++) r[i] = S[i];
-   }
+   int calls;                   // rhs() evaluations: (2 nEq + 1) per step + 3 per attempt, a signature of the step sequence
+   __device__ void rhs(double *r, const double *x) { calls++; chemRhs(r, x, S, &T); }
 };
 
 // In-place LU factorisation with implicit-scaling partial pivoting (Crout) and solve.
@@ -126,7 +133,7 @@ struct LU {
    double A[n*n];
    int ind[n];
    __device__ double &a(int i, int j) { return A[i + j*n]; }
-   __device__ void factor() {
+   __device__ __noinline__ void factor() {
       int imax = 0;
       double vv[n];
       for (int i = 0; i < n; i++) {
@@ -160,7 +167,7 @@ struct LU {
          }
       }
    }
-   __device__ void solve(double *b) {
+   __device__ __noinline__ void solve(double *b) {
       int ii = 0;
       for (int i = 0; i < n; i++) {
          const int ip = ind[i];
@@ -194,12 +201,14 @@ __device__ bool rosenbrockSolve(Problem &prob, double *x, double dtTry, double D
    bool finish = false;
    double time = 0.0;
    double dt = dtTry;
+   #pragma unroll 1
    for (int s = 0; s < MAXSTP; s++) {
       const double t0 = time;
       double dtNext = 0.0;
       {  // Jacobian by central differences, step x_j*1e-6 + 1e-14
          double tmp[n], fp[n], fm[n];
          for (int i = 0; i < n; i++) tmp[i] = x[i];
+         #pragma unroll 1
          for (int j = 0; j < n; j++) {
             const double h = x[j]*1.0e-6 + 1.0e-14;
             x[j] = tmp[j] + h;
@@ -215,6 +224,7 @@ __device__ bool rosenbrockSolve(Problem &prob, double *x, double dtTry, double D
       prob.rhs(dx, x);
       for (int i = 0; i < n; i++) { xsav[i] = x[i]; dxsav[i] = dx[i]; }
       bool converged = false;
+      #pragma unroll 1
       for (int jtry = 0; jtry < MAXITS; jtry++) {
          double g1[n], g2[n], g3[n], g4[n];
          for (int i = 0; i < n; i++) {

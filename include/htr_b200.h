@@ -101,6 +101,9 @@ int htr_update_chemistry(const htr_fluid *f, const htr_rect *tile, double Integr
 /* Cells whose implicit integration hit the step/iteration caps since the last call (the reference
  * asserts there, src/Utils/math_utils.hpp:233,240).  Synchronises the device and resets the counter. */
 int htr_chemistry_failures(void);
+/* diagnostic (parity tests): htr_update_chemistry then also writes the number of right-hand-side evaluations of every
+ * cell of its tile (dense int32, x fastest) to the DEVICE buffer d_counts; NULL switches it off. */
+int htr_chemistry_rhs_counts(int *d_counts);
 /* the same after synchronising `stream`, the stream the update was launched on (any kind of stream) */
 int htr_chemistry_failures_on(void *stream);
 /* 1 if htr_set_mixture has been called on the CURRENT device (all library state is per device: one process may drive

@@ -415,6 +415,54 @@ void htr_oracle_update_chemistry(const htr_oracle_fields *f, double dt) {
          }
 }
 
+// The same task with the number of rhs() evaluations of every cell reported: (2 nEq + 1) per integration step plus 3
+// per step attempt, i.e. a signature of the adaptive step / retry sequence (tests compare it with the GPU kernel's).
+// rhs() below restates ImplicitSolver::rhs (src/prometeo_chem.hpp:66-87), which is private there.
+namespace { class CountingSolver : public Rosenbrock<nEq> {
+public:
+   CountingSolver(const VecNEq &S_, double &T_, const Mix &m_) : calls(0), S(S_), temperature(T_), m(m_) {}
+   int calls;
+private:
+   inline void rhs(VecNEq &r, const VecNEq &x) {
+      calls++;
+      VecNSp rhoYi;
+      for (int i = 0; i < nSpec; i++) rhoYi[i] = x[i];
+      const double rho = m.GetRhoFromRhoYi(rhoYi);
+      VecNSp Yi; m.GetYi(Yi, rho, rhoYi);
+      m.ClipYi(Yi);
+      const double MixW = m.GetMolarWeightFromYi(Yi);
+      const double rhoInv = 1.0/rho;
+      Vec3 velocity;
+      for (int i = 0; i < 3; i++) velocity[i] = x[i + irU]*rhoInv;
+      const double kineticEnergy = 0.5*velocity.mod2();
+      const double InternalEnergy = x[irE]*rhoInv - kineticEnergy;
+      temperature = m.GetTFromInternalEnergy(InternalEnergy, temperature, Yi);
+      const double pressure = m.GetPFromRhoAndT(rho, MixW, temperature);
+      VecNSp w; m.GetProductionRates(w, rho, pressure, temperature, Yi);
+      for (int i = 0; i < nSpec; i++) r[i] = w[i] + S[i];
+      for (int i = nSpec; i < nEq; i++) r[i] = S[i];
+   }
+   const VecNEq &S; double &temperature; const Mix &m;
+}; }
+void htr_oracle_update_chemistry_counted(const htr_oracle_fields *f, double dt, int *rhs_calls) {
+   Acc a(f);
+   const AccessorRO<VecNEq, 3> Ct = a.ro<VecNEq>(f->Conserved_t);
+   const AccessorRW<VecNEq, 3> C = a.rw<VecNEq>(f->Conserved), Cto = a.rw<VecNEq>(f->Conserved_t_old);
+   const AccessorRW<double, 3> T = a.rw<double>(f->temperature);
+#ifdef _OPENMP
+   #pragma omp parallel for collapse(3) schedule(dynamic, 16)
+#endif
+   for (int k = 0; k < a.nz; k++)
+      for (int j = 0; j < a.ny; j++)
+         for (int i = 0; i < a.nx; i++) {
+            const Point<3> p(i, j, k);
+            Cto[p] = Ct[p];
+            CountingSolver s(Cto[p], T[p], mix());
+            s.solve(C[p], dt, dt);
+            rhs_calls[(k*a.ny + j)*a.nx + i] = s.calls;
+         }
+}
+
 // src/prometeo_variables.cc:138-173
 void htr_oracle_update_primitive_from_conserved(const htr_oracle_fields *f) {
    Acc a(f);

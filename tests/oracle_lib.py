@@ -157,6 +157,14 @@ class Oracle:
     def update_chemistry(self, f, dt):
         self.lib.htr_oracle_update_chemistry(C.byref(self._struct(f)), dt)
 
+    def update_chemistry_counted(self, f, dt):
+        """UpdateChemistry + the number of rhs() evaluations of every cell (signature of its step sequence)."""
+        nz, ny, nx = f["rho"].shape
+        calls = np.zeros((nz, ny, nx), dtype=np.int32)
+        self.lib.htr_oracle_update_chemistry_counted.argtypes = [C.c_void_p, C.c_double, C.c_void_p]
+        self.lib.htr_oracle_update_chemistry_counted(C.byref(self._struct(f)), dt, calls.ctypes.data)
+        return calls
+
     def update_primitive_from_conserved(self, f):
         self.lib.htr_oracle_update_primitive_from_conserved(C.byref(self._struct(f)))
 

@@ -140,25 +140,52 @@ def test_chemistry_sources():
 
 @pytest.mark.parametrize("variant", ["", "strict"], ids=["prod", "strict"])
 def test_update_chemistry(variant):
-    o = oracle_for(AIR)
-    f = host_state(o, (8, 6, 4), AIR, species_wave=1.0, T0=9.0)
+    """UpdateChemistry (adaptive Rosenbrock-4 with a finite-difference Jacobian, src/prometeo_chem.hpp:53-92,
+    src/Utils/math_utils.hpp:196-441) on a 32^3 hot AirMix box with a temperature front and radicals, against the
+    reference's task.  The integrator is ADAPTIVE (step size ~ errmax^-1/4 with errmax = local error / 1e-10): two
+    evaluations that differ in the last bit of an exp can accept / reject a different step, after which the two results
+    differ by the integrator's tolerance, not by round-off.  So the comparison is split: cells whose number of
+    right-hand-side evaluations (2 nEq + 1 per step + 3 per attempt: a signature of the step sequence) equals the
+    reference's must agree to 1e-10 (north-star tolerance with chemistry); the others to the tolerance class 1e-8, and
+    their count is printed and bounded."""
+    cfg = AIR
+    from oracle_lib import Oracle
+    try:                                          # ~100 adaptive steps per cell: the OpenMP build of the same sources
+        o = Oracle(cfg["type"], omp=True, kind="reference")
+        o.init_mix(cfg)
+    except FileNotFoundError:
+        o = oracle_for(cfg)
+    n = (32, 32, 32)
+    f = host_state(o, n, cfg, species_wave=1.0, front=0.3, p0=1.0, T0=6.0, U=0.5)
     f["Conserved_t"][...] = 0.0
-    s = htr.Solver(AIR, variant=variant)
+    o.add_chemistry_sources(f)                    # a non-trivial frozen explicit part
+    f["Conserved_t"] *= 0.1
+    import torch
+    s = htr.Solver(cfg, variant=variant)
     fl = to_device(s, f)
-    dt = 1e-3
     before = f["Conserved"].copy()
-    o.update_chemistry(f, dt)
-    s.UpdateChemistry(fl, dt)
+    dt = 2e-3
+    calls_ref = o.update_chemistry_counted(f, dt)
+    calls = torch.zeros(n[::-1], dtype=torch.int32, device="cuda")
+    s.UpdateChemistry(fl, dt, rhs_counts=calls)
+    calls = calls.cpu().numpy()
     got = fl.download(["Conserved", "temperature", "Conserved_t_old"])
     assert rel_err(before[..., :5], f["Conserved"][..., :5]) > 1e-3, "chemistry must be active in this test"
-    # the adaptive integrator controls its local error to TOL=1e-10 (src/Utils/math_utils.hpp:391) and its
-    # finite-difference Jacobian amplifies last-digit differences of exp/log/pow by 1/h = 1e6:
-    # agreement is to the integrator's tolerance class, not to round-off
-    # `temperature` leaves the task as the Newton iterate of the LAST rhs() call, i.e. at the third-stage
-    # state of the last Rosenbrock step (src/prometeo_chem.hpp:66-87): it depends on the adaptive step
-    # sequence (dtNext ~ errmax^-1/4, errmax = noise-level error / 1e-10) and is only a Newton guess.
-    eC, eT = rel_err(got["Conserved"], f["Conserved"]), rel_err(got["temperature"], f["temperature"])
-    assert eC <= 1e-9 and eT <= 1e-5, (eC, eT)
+    assert np.array_equal(got["Conserved_t_old"], f["Conserved_t_old"])
+    same = calls == calls_ref
+    nd = int((~same).sum())
+    scale = np.abs(f["Conserved"]).reshape(-1, 9).max(axis=0)
+    err = np.abs(got["Conserved"] - f["Conserved"])/scale
+    e_same = float(err[same].max())
+    e_diff = float(err[~same].max()) if nd else 0.0
+    eT = float((np.abs(got["temperature"] - f["temperature"])/np.abs(f["temperature"]))[same].max())
+    print(f"UpdateChemistry {variant or 'prod'}: rhs evaluations per cell {calls_ref.min()}..{calls_ref.max()}, "
+          f"{nd} of {same.size} cells took a different step sequence; max error {e_same:.2e} (same sequence), "
+          f"{e_diff:.2e} (different), temperature {eT:.2e}")
+    assert e_same <= 1e-10, e_same
+    assert eT <= 1e-10, eT
+    assert e_diff <= 1e-8, e_diff
+    assert nd <= 0.02*same.size, nd
 
 
 @pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "SkewSymmetric", False, {}), (CP, "Hybrid", False, {"front": 0.3}),
