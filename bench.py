@@ -31,7 +31,10 @@ WORKLOADS = {
     "air512_front":  ("AIRMIX_3DPERIODIC", 512, "Hybrid", True, True,  "solverTests/3DPeriodic_Air/base.json scaled to 512^3 + tanh front (front=0.3, T0=6, U=0.5)"),
     "air256_front":  ("AIRMIX_3DPERIODIC", 256, "Hybrid", True, True,  "solverTests/3DPeriodic_Air/base.json scaled to 256^3 + tanh front (front=0.3, T0=6, U=0.5)"),
 }
-IC_KW = {"air512_front": {"front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5}, "air256_front": {"front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5}}
+    # BASELINE config C5: y stretched with the reference's Tanh map (testcases/scalingTest/WeakScaling/base.json, Stretching
+    # 1.3844), metrics by the reference's InitializeMetricTask (fixture tests/golden/tanh_y_metrics.npz), periodic in y for now
+WORKLOADS["air512_tanh"] = ("AIRMIX_3DPERIODIC", 512, "Hybrid", True, True, "testcases/scalingTest/WeakScaling/base.json grid (Tanh in y, 512^3 per GPU) with the 3DPeriodic_Air flow")
+IC_KW = {"air512_tanh": {"ygrid": "tanh"}, "air512_front": {"front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5}, "air256_front": {"front": 0.3, "T0": 6.0, "p0": 1.0, "U": 0.5}}
 DEFAULT_WORKLOAD = "air512"
 
 
@@ -119,6 +122,15 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def tanh_ygrid(gny):
+    """Cell centres and y metrics of the Tanh-stretched direction from the committed fixture (generated with the reference's
+    own metric code by tests/golden/gen_tanh_metrics.py)."""
+    d = np.load(os.path.join(ROOT, "tests", "golden", "tanh_y_metrics.npz"))
+    if f"ny{gny}_centers" not in d:
+        raise SystemExit(f"no Tanh fixture for {gny} cells in y (tests/golden/gen_tanh_metrics.py makes 40, 512, 1024)")
+    return {k: d[f"ny{gny}_{k}"] for k in ("centers", "deta_e", "deta_d", "deta_s")}
+
+
 def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32, ic_kw=None):
     """Synthetic Taylor-Green primitives generated slab by slab on the host, uploaded into the block
     (interior + halo, which for a periodic global box is just more of the same analytic field), then
@@ -128,6 +140,9 @@ def fill_block(solver, fl, cfg, n, offset, global_n, halo, slab=32, ic_kw=None):
     nx = ny = nz = n
     h = halo
     tot = n + 2 * h
+    ic_kw = dict(ic_kw or {})
+    if ic_kw.get("ygrid") == "tanh":
+        ic_kw["ygrid"] = tanh_ygrid(global_n[1])
     for k0 in range(0, tot, slab):
         k1 = min(tot, k0 + slab)
         f = synthetic.taylor_green((tot, tot, tot), cfg, zslab=(k0, k1), species_wave=1.0 if cfg["type"] != "ConstPropMix" else 0.0,
@@ -162,7 +177,11 @@ def cpu_reference_arm(cfgname, scheme, diffusion, chemistry, budget_s=20.0, n=No
     if n is None:
         n = 160 if mix != "ConstPropMix" else 192
     f = alloc_fields(n, n, n, o.nspec)
-    prim = synthetic.taylor_green(n, cfg, species_wave=1.0 if mix != "ConstPropMix" else 0.0, **(ic_kw or {}))
+    ic_kw = dict(ic_kw or {})
+    if ic_kw.get("ygrid") == "tanh":          # the sample box gets its own Tanh grid, metrics by the reference's code
+        from oracle_lib import tanh_y_metrics
+        ic_kw["ygrid"] = tanh_y_metrics(o, n)
+    prim = synthetic.taylor_green(n, cfg, species_wave=1.0 if mix != "ConstPropMix" else 0.0, **ic_kw)
     for k, v in prim.items():
         f[k][...] = v
     o.update_properties_from_primitive(f)

@@ -478,7 +478,12 @@ __device__ int d_chem_failures;
 
 __device__ int *d_chem_calls;      // optional diagnostic output (htr_chemistry_rhs_counts): rhs() evaluations per cell of the tile
 
-__global__ void __launch_bounds__(128) update_chemistry_kernel(const htr_fluid f, const htr_rect tile, const double dt) {
+// resident CTAs per SM the register allocation aims at: the integration is a long chain of dependent fp64 operations
+// (top stall: fixed-latency `wait`), so it wants warps more than registers; its state lives in local memory anyway
+#ifndef HTR_CHEM_MINB
+#define HTR_CHEM_MINB 4
+#endif
+__global__ void __launch_bounds__(128, HTR_CHEM_MINB) update_chemistry_kernel(const htr_fluid f, const htr_rect tile, const double dt) {
    Pt p; if (!cellOf(p, tile)) return;
    double S[nEq], x[nEq];
    const double *Ct = at<const double>(f.Conserved_t, p);

@@ -23,8 +23,33 @@ CH41ST_3DPERIODIC = {"type": "CH41StMix", "LRef": 1.0, "TRef": 300.0, "PRef": 10
 SPECIES = {"AirMix": AIR_SPECIES, "CH41StMix": ["CH4", "O2", "CO2", "H2O"]}
 
 
+def grid_nodes(n, origin, width, kind="Uniform", stretching=1.0):
+    """Node positions of one direction as the reference places them (src/prometeo_grid.rg:123-230: InitializeNodeGrid +
+    transform_uniform_to_nonuniform): n+1 nodes on [origin, origin+width], uniform or mapped by the Tanh family."""
+    xmin, xmax = origin, origin + width
+    u = xmin + np.arange(n + 1) * ((xmax - xmin) / n)
+    lin = lambda x, x0, x1, y0, y1: y0 + (x - x0) * (y1 - y0) / (x1 - x0)
+    if kind == "Uniform":
+        return u
+    if kind == "Tanh":
+        s = lin(u, xmin, xmax, -1.0, 1.0)
+        return lin(np.tanh(stretching * s) / np.tanh(stretching), -1.0, 1.0, xmin, xmax)
+    if kind == "TanhMinus":
+        s = lin(u, xmin, xmax, -1.0, 0.0)
+        return lin(np.tanh(stretching * s) / np.tanh(stretching), -1.0, 0.0, xmin, xmax)
+    if kind == "TanhPlus":
+        s = lin(u, xmin, xmax, 0.0, 1.0)
+        return lin(np.tanh(stretching * s) / np.tanh(stretching), 0.0, 1.0, xmin, xmax)
+    raise ValueError(kind)
+
+
+def cell_centers(nodes):
+    """Interior cell centres (src/prometeo_grid.rg:313-316): the mean of the two nodes."""
+    return 0.5 * (nodes[1:] + nodes[:-1])
+
+
 def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=0.0, species_wave=0.0,
-                 front=0.0, dtype=np.float64, zslab=None, offset=(0, 0, 0), global_n=None):
+                 front=0.0, dtype=np.float64, zslab=None, offset=(0, 0, 0), global_n=None, ygrid=None):
     """Host fields of an (nx,ny,nz)=n periodic box.  Returns dict name -> array [z][y][x](comp).
 
     stretch > 0      multiplies the metrics by 1 + stretch*sin(coordinate): a smooth non-uniform grid
@@ -46,6 +71,12 @@ def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=
     y = (np.arange(ny) + offset[1] + 0.5) * width / gy
     z = (np.arange(k0, k1) + offset[2] + 0.5) * width / gz
     nz = k1 - k0
+    if ygrid is not None:
+        # y stretched like the reference's grids: cell centres and the three y metrics of the GLOBAL (periodic) direction come
+        # from the caller (dict: centers, deta_e, deta_d, deta_s, each of length gy: the reference's InitializeMetricTask
+        # evaluated through the oracle by tests/golden/gen_tanh_metrics.py, or a committed fixture of it)
+        jy = (np.arange(ny) + offset[1]) % gy
+        y = np.asarray(ygrid["centers"])[jy]
     Z, Y, X = np.meshgrid(z, y, x, indexing="ij")
     f = {}
     for d, (nn, c) in enumerate(((gx, X), (gy, Y), (gz, Z))):
@@ -53,6 +84,9 @@ def taylor_green(n, mix_cfg, p0=None, T0=None, U=None, width=2 * np.pi, stretch=
         for kind in "eds":
             f[("dcsi_", "deta_", "dzet_")[d] + kind] = np.ascontiguousarray(m * (1.0 + 0.01 * stretch * "eds".index(kind)))
         f[("nType_x", "nType_y", "nType_z")[d]] = np.zeros((nz, ny, nx), dtype=np.int32)
+    if ygrid is not None:
+        for kind in "eds":
+            f["deta_" + kind] = np.ascontiguousarray(np.broadcast_to(np.asarray(ygrid["deta_" + kind])[jy][None, :, None], (nz, ny, nx)))
     R = mix_cfg.get("gasConstant", 1.0)
     rho0 = p0 / (R * T0)
     vel = np.zeros((nz, ny, nx, 3))

@@ -87,6 +87,8 @@ void htr_oracle_rosenbrock3(double *x3, double dt, double dtTry);
 /* Number of OpenMP threads the library was built to use (1 when serial). */
 int htr_oracle_max_threads(void);
 void htr_oracle_update_chemistry_counted(const htr_oracle_fields *f, double dt, int *rhs_calls);   /* + rhs() evaluations per cell */
+/* InitializeMetricTask (src/prometeo_metric.cc:36-190): all nine metric fields from cell-centre coordinates [z][y][x][3] */
+void htr_oracle_initialize_metric(const htr_oracle_fields *f, const double *centerCoordinates, const double *width);
 void htr_oracle_set_threads(int n);      /* OpenMP threads of the timed build (bench.py: all host cores, also under torchrun) */
 #ifdef __cplusplus
 }

@@ -20,7 +20,9 @@ using namespace Legion;
 // prometeo_rhs.inl and prometeo_sensor.inl, so (like the reference, which builds
 // prometeo_rhs.cc and prometeo_sensor.cc separately) this file is compiled twice:
 // plain (rhs + mixture), -DHTR_PART_SENSOR and -DHTR_PART_VARS (variables, chem, cfl).
-#if defined(HTR_PART_SENSOR)
+#if defined(HTR_PART_METRIC)
+#include "prometeo_metric.hpp"
+#elif defined(HTR_PART_SENSOR)
 #include "prometeo_sensor.hpp"
 #include "prometeo_sensor.inl"
 #elif defined(HTR_PART_VARS)
@@ -37,6 +39,77 @@ using namespace Legion;
 #define HTR_STR2(x) #x
 #define HTR_STR(x) HTR_STR2(x)
 
+#if defined(HTR_PART_METRIC)
+// src/prometeo_metric.cc:36-190 (InitializeMetricTask::cpu_base_impl): the nine metric fields of a box from its cell-centre
+// coordinates, with the reference's own reconstructCoordEuler / ComputeDiffusionMetrics (src/prometeo_metric.hpp:113-160);
+// the box is the whole (periodic or bounded, per nType) domain.  centerCoordinates: [z][y][x][3] doubles.
+extern "C" void htr_oracle_initialize_metric(const htr_oracle_fields *f, const double *centerCoordinates, const double *width) {
+   const coord_t nx = f->nx, ny = f->ny, nz = f->nz;
+   const Rect<3> B(Point<3>(0, 0, 0), Point<3>(nx - 1, ny - 1, nz - 1));
+   const coord_t sv = sizeof(Vec3), sd = sizeof(double), si = sizeof(int);
+   const AccessorRO<Vec3, 3> cc((void*)centerCoordinates, sv, sv*nx, sv*nx*ny);
+   const AccessorRO<int, 3> tx((void*)f->nType_x, si, si*nx, si*nx*ny), ty((void*)f->nType_y, si, si*nx, si*nx*ny), tz((void*)f->nType_z, si, si*nx, si*nx*ny);
+   #define HTR_WO(name) const AccessorWO<double, 3> name((void*)f->name, sd, sd*nx, sd*nx*ny)
+   HTR_WO(dcsi_e); HTR_WO(deta_e); HTR_WO(dzet_e); HTR_WO(dcsi_d); HTR_WO(deta_d); HTR_WO(dzet_d); HTR_WO(dcsi_s); HTR_WO(deta_s); HTR_WO(dzet_s);
+   #undef HTR_WO
+   typedef InitializeMetricTask M;
+   const coord_t xsize = getSize<Xdir>(B), ysize = getSize<Ydir>(B), zsize = getSize<Zdir>(B);
+   for (int k = 0; k < nz; k++)
+      for (int j = 0; j < ny; j++) {
+         double xM_e, xP_e;
+         {
+            const Point<3> p(0, j, k);
+            const Point<3> pm1 = warpPeriodic<Xdir, Minus>(B, p, xsize, offM1(tx[p]));
+            xM_e = M::reconstructCoordEuler<Xdir>(cc, pm1, width[0], tx[pm1], xsize, B);
+            xM_e = unwarpCoordinate<Xdir>(xM_e, width[0], -1, p, B);
+         }
+         for (int i = 0; i < nx; i++) {
+            const Point<3> p(i, j, k);
+            xP_e = M::reconstructCoordEuler<Xdir>(cc, p, width[0], tx[p], xsize, B);
+            dcsi_e[p] = 1.0/(xP_e - xM_e);
+            M::ComputeDiffusionMetrics<Xdir>(dcsi_d, dcsi_s, cc, p, width[0], tx[p], xsize, B);
+            xM_e = xP_e;
+         }
+      }
+   for (int k = 0; k < nz; k++)
+      for (int i = 0; i < nx; i++) {
+         double yM_e, yP_e;
+         {
+            const Point<3> p(i, 0, k);
+            const Point<3> pm1 = warpPeriodic<Ydir, Minus>(B, p, ysize, offM1(ty[p]));
+            yM_e = M::reconstructCoordEuler<Ydir>(cc, pm1, width[1], ty[pm1], ysize, B);
+            yM_e = unwarpCoordinate<Ydir>(yM_e, width[1], -1, p, B);
+         }
+         for (int j = 0; j < ny; j++) {
+            const Point<3> p(i, j, k);
+            yP_e = M::reconstructCoordEuler<Ydir>(cc, p, width[1], ty[p], ysize, B);
+            deta_e[p] = 1.0/(yP_e - yM_e);
+            M::ComputeDiffusionMetrics<Ydir>(deta_d, deta_s, cc, p, width[1], ty[p], ysize, B);
+            yM_e = yP_e;
+         }
+      }
+   for (int j = 0; j < ny; j++)
+      for (int i = 0; i < nx; i++) {
+         double zM_e, zP_e;
+         {
+            const Point<3> p(i, j, 0);
+            const Point<3> pm1 = warpPeriodic<Zdir, Minus>(B, p, zsize, offM1(tz[p]));
+            zM_e = M::reconstructCoordEuler<Zdir>(cc, pm1, width[2], tz[pm1], zsize, B);
+            zM_e = unwarpCoordinate<Zdir>(zM_e, width[2], -1, p, B);
+         }
+         for (int k = 0; k < nz; k++) {
+            const Point<3> p(i, j, k);
+            zP_e = M::reconstructCoordEuler<Zdir>(cc, p, width[2], tz[p], zsize, B);
+            dzet_e[p] = 1.0/(zP_e - zM_e);
+            M::ComputeDiffusionMetrics<Zdir>(dzet_d, dzet_s, cc, p, width[2], tz[p], zsize, B);
+            zM_e = zP_e;
+         }
+      }
+}
+#define HTR_METRIC_ONLY 1
+#endif
+
+#ifndef HTR_METRIC_ONLY
 #if defined(HTR_PART_SENSOR) || defined(HTR_PART_VARS)
 extern Mix *htr_ref_g_mix;
 #else
@@ -562,3 +635,4 @@ void htr_oracle_ducros_sensor(const htr_oracle_fields *f, double vorticityScale)
 
 #endif
 } // extern "C"
+#endif // HTR_METRIC_ONLY

@@ -51,6 +51,9 @@ namespace Legion {
       Point(T x_, T y_, T z_) : x(x_), y(y_), z(z_) {}
       T operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
    };
+   template<typename T> inline Point<3, T> operator+(const Point<3, T> &a, const Point<3, T> &b) { return Point<3, T>(a.x + b.x, a.y + b.y, a.z + b.z); }
+   template<typename T> inline Point<3, T> operator-(const Point<3, T> &a, const Point<3, T> &b) { return Point<3, T>(a.x - b.x, a.y - b.y, a.z - b.z); }
+   template<typename T> inline bool operator==(const Point<3, T> &a, const Point<3, T> &b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
    template<int N, typename T = coord_t> struct Rect {
       Point<N, T> lo, hi;
       Rect() {}

@@ -157,6 +157,14 @@ class Oracle:
     def update_chemistry(self, f, dt):
         self.lib.htr_oracle_update_chemistry(C.byref(self._struct(f)), dt)
 
+    def initialize_metric(self, f, centers, width):
+        """InitializeMetricTask (src/prometeo_metric.cc:36-190): fills the nine metric fields of `f` from the cell-centre
+        coordinates `centers` [z][y][x][3] of a box of physical size `width`, node types taken from f."""
+        centers = np.ascontiguousarray(centers, dtype=np.float64)
+        w = np.ascontiguousarray(width, dtype=np.float64)
+        self.lib.htr_oracle_initialize_metric.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.htr_oracle_initialize_metric(C.byref(self._struct(f)), centers.ctypes.data, w.ctypes.data)
+
     def update_chemistry_counted(self, f, dt):
         """UpdateChemistry + the number of rhs() evaluations of every cell (signature of its step sequence)."""
         nz, ny, nx = f["rho"].shape
@@ -188,3 +196,19 @@ class Oracle:
         if diffusion:
             for d in (2, 1, 0):
                 self.diffusion_flux(f, d)
+
+
+def tanh_y_metrics(o, ny, stretching=1.3843992415368547, width=2 * np.pi):
+    """Cell centres and y metrics of a periodic direction whose nodes follow the reference's Tanh map
+    (src/prometeo_grid.rg:123-230), metrics by the reference's InitializeMetricTask through the oracle `o`."""
+    import sys
+    sys.path.insert(0, ROOT)
+    from htr_solver_b200 import synthetic
+    nodes = synthetic.grid_nodes(ny, 0.0, width, "Tanh", stretching)
+    yc = synthetic.cell_centers(nodes)
+    f = alloc_fields(1, ny, 1, o.nspec)              # a line: the metrics are separable
+    cc = np.zeros((1, ny, 1, 3))
+    cc[0, :, 0, 1] = yc
+    cc[..., 0] = 0.5 * width; cc[..., 2] = 0.5 * width
+    o.initialize_metric(f, cc, [width, width, width])
+    return dict(centers=yc, deta_e=f["deta_e"][0, :, 0].copy(), deta_d=f["deta_d"][0, :, 0].copy(), deta_s=f["deta_s"][0, :, 0].copy())

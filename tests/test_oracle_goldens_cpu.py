@@ -230,3 +230,33 @@ def test_mixtest_ch41stmix_goldens():
         chk(r["dpdrhoi"][i] * q["eRef"], e, f"dpdrhoi[{i}]")
     for i, e in enumerate([-3.294307e+06, 4.425045e+05, -8.481094e+06, -1.253075e+07]):
         chk(o.lib.htr_oracle_species_enthalpy(i, T / 300.0) * q["eRef"], e, f"hsp[{i}]")
+
+
+@needs_cp
+def test_metrics_uniform_grid_and_tanh_fixture():
+    """InitializeMetricTask through the oracle: on a uniform periodic grid all nine metrics are 1/dx to round-off
+    (SURVEY appendix A); the committed Tanh fixture (tests/golden/tanh_y_metrics.npz, read by bench.py's air512_tanh
+    workload) is what the reference's code gives for those nodes."""
+    import os
+    from oracle_lib import tanh_y_metrics
+    from htr_solver_b200 import synthetic
+    o = Oracle("ConstPropMix")
+    n, w = (12, 10, 8), 2 * np.pi
+    f = alloc_fields(*n, 1)
+    cc = np.zeros(n[::-1] + (3,))
+    for d, nn in enumerate(n):
+        c = synthetic.cell_centers(synthetic.grid_nodes(nn, 0.0, w))
+        shape = [1, 1, 1]; shape[2 - d] = nn
+        cc[..., d] = c.reshape(shape)
+    o.initialize_metric(f, cc, [w, w, w])
+    for d, nn in enumerate(n):
+        for kind in "eds":
+            m = f[("dcsi_", "deta_", "dzet_")[d] + kind]
+            assert np.allclose(m, nn / w, rtol=1e-13), (d, kind)
+    fix = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tanh_y_metrics.npz"))
+    m = tanh_y_metrics(o, 40, float(fix["stretching"]), float(fix["width"]))
+    for k, v in m.items():
+        assert np.array_equal(v, fix[f"ny40_{k}"]), k
+    # Tanh: small cells at both ends, symmetric, sizes sum to the width
+    dy = 1.0 / m["deta_e"]
+    assert abs(dy.sum() - float(fix["width"])) < 1e-12 and dy[0] < 0.3 * dy[20] and abs(dy[3] / dy[-4] - 1) < 1e-10

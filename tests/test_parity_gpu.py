@@ -174,18 +174,25 @@ def test_update_chemistry(variant):
     assert np.array_equal(got["Conserved_t_old"], f["Conserved_t_old"])
     same = calls == calls_ref
     nd = int((~same).sum())
-    scale = np.abs(f["Conserved"]).reshape(-1, 9).max(axis=0)
-    err = np.abs(got["Conserved"] - f["Conserved"])/scale
+    # partial densities and total energy change; the momentum components are only carried (zero source)
+    scale = np.maximum(np.abs(f["Conserved"]).reshape(-1, 9).max(axis=0), 1e-300)
+    err = (np.abs(got["Conserved"] - f["Conserved"])/scale).max(axis=-1)
     e_same = float(err[same].max())
     e_diff = float(err[~same].max()) if nd else 0.0
-    eT = float((np.abs(got["temperature"] - f["temperature"])/np.abs(f["temperature"]))[same].max())
+    errT = np.abs(got["temperature"] - f["temperature"])/np.abs(f["temperature"])
+    eT = float(errT[same].max())
+    q = np.quantile(err[same], [0.5, 0.99, 0.9999])
+    qT = np.quantile(errT[same], [0.5, 0.99, 0.9999])
     print(f"UpdateChemistry {variant or 'prod'}: rhs evaluations per cell {calls_ref.min()}..{calls_ref.max()}, "
-          f"{nd} of {same.size} cells took a different step sequence; max error {e_same:.2e} (same sequence), "
-          f"{e_diff:.2e} (different), temperature {eT:.2e}")
+          f"{nd} of {same.size} cells took a different step sequence; Conserved: max error {e_same:.2e} (same sequence; median {q[0]:.1e}, "
+          f"99% {q[1]:.1e}, 99.99% {q[2]:.1e}), {e_diff:.2e} (different sequence); temperature (same sequence): max {eT:.2e}, "
+          f"median {qT[0]:.1e}, 99% {qT[1]:.1e}, 99.99% {qT[2]:.1e}; cells above 1e-10: {int((err[same] > 1e-10).sum())} / T {int((errT[same] > 1e-10).sum())}")
     assert e_same <= 1e-10, e_same
-    assert eT <= 1e-10, eT
     assert e_diff <= 1e-8, e_diff
     assert nd <= 0.02*same.size, nd
+    # `temperature` leaves the task as the Newton iterate of the LAST rhs() evaluation (third-stage state of the last
+    # step, src/prometeo_chem.hpp:66-87): a Newton guess for the next primitive update, stopped at |dT| < 1e-8
+    assert eT <= 1e-7, eT
 
 
 @pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "SkewSymmetric", False, {}), (CP, "Hybrid", False, {"front": 0.3}),
@@ -248,6 +255,31 @@ def test_full_rhs_at_baseline_grid_sizes(cfg, scheme, chem, n, kw):
     smooth = float(np.mean(f["shockSensorX"])) if scheme == "Hybrid" else None
     print(f"{cfg['type']} {scheme} {n}: max scaled error {e:.3e}, by max|ref| {rel_err(got, f['Conserved_t']):.3e}, smooth fraction {smooth}")
     assert e <= (TOL_CHEM if chem else TOL_FLUX), e
+
+
+@pytest.mark.parametrize("scheme", ["Hybrid", "TENO"])
+def test_full_rhs_on_the_tanh_stretched_grid(scheme):
+    """BASELINE config C5's grid: y nodes on the reference's Tanh map (Stretching 1.3844, cell sizes varying 4.2x), metrics by
+    the reference's InitializeMetricTask (fixture tests/golden/tanh_y_metrics.npz); AirMix RHS with diffusion and chemistry."""
+    import os
+    fix = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "tanh_y_metrics.npz"))
+    ygrid = {k: fix[f"ny40_{k}"] for k in ("centers", "deta_e", "deta_d", "deta_s")}
+    cfg, n = AIR, (24, 40, 16)
+    o = oracle_for(cfg)
+    f = host_state(o, n, cfg, species_wave=1.0, front=0.3, ygrid=ygrid)
+    assert f["deta_e"].max() / f["deta_e"].min() > 4.0
+    _sensors(o, f)
+    s = htr.Solver(cfg)
+    fl = to_device(s, f)
+    o.rhs(f, scheme, diffusion=True, chemistry=True, RK0=1.0, RK1=0.0, dt=1e-3)
+    s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=True, RK_coeffs=(1.0, 0.0), deltaTime=1e-3)
+    got = fl.download(["Conserved_t"])["Conserved_t"]
+    scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
+    ref = f["Conserved_t"].copy()
+    f["Conserved_t"][...] = 0.0
+    o.add_chemistry_sources(f)
+    scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
+    assert scaled_err(got, ref, scale) <= TOL_CHEM
 
 
 @pytest.mark.parametrize("cfg,scheme,chem,kw", [(CP, "Hybrid", False, {"front": 0.3}), (AIR, "Hybrid", True, {"species_wave": 1.0})],

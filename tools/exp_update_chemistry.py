@@ -6,7 +6,7 @@ import htr_solver_b200 as htr
 from htr_solver_b200 import synthetic
 cfg = synthetic.AIRMIX_3DPERIODIC
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 96
-s = htr.Solver(cfg)
+s = htr.Solver(cfg, variant=(sys.argv[2] if len(sys.argv) > 2 else ''))
 fl = s.new_fluid(n, n, n)
 f = synthetic.taylor_green((n, n, n), cfg, species_wave=1.0, front=0.2, p0=1.0, T0=6.0, U=0.5)
 for name, arr in f.items():
