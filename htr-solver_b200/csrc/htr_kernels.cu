@@ -481,7 +481,7 @@ __device__ int *d_chem_calls;      // optional diagnostic output (htr_chemistry_
 // resident CTAs per SM the register allocation aims at: the integration is a long chain of dependent fp64 operations
 // (top stall: fixed-latency `wait`), so it wants warps more than registers; its state lives in local memory anyway
 #ifndef HTR_CHEM_MINB
-#define HTR_CHEM_MINB 4
+#define HTR_CHEM_MINB 6      // B200, 96^3 hot AirMix box: 695 ms at 2, 588 ms at 4, 541 ms at 6 (902 ms before rhs() went out of line)
 #endif
 __global__ void __launch_bounds__(128, HTR_CHEM_MINB) update_chemistry_kernel(const htr_fluid f, const htr_rect tile, const double dt) {
    Pt p; if (!cellOf(p, tile)) return;
@@ -1484,3 +1484,6 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
 }
 
 } // extern "C"
+
+// ghost-plane exchange over NCCL + scalar max-reduction (htr_comm_*, htr_halo_exchange, htr_allreduce_max)
+#include "htr_halo.cuh"

@@ -59,7 +59,8 @@ def phase_slices(n, d, h=HALO):
 
 
 def exchange(tensors, n, rank, tiles, dist=None, h=HALO):
-    """Fills the ghost planes of every tensor in `tensors` ([z][y][x](comp), h ghosts per side).
+    """Host-logic double of Comm.exchange in plain torch (CPU tests with gloo, tests/test_halo_cpu.py; the GPU path is the
+    C++ exchange).  Fills the ghost planes of every tensor in `tensors` ([z][y][x](comp), h ghosts per side).
     Runs on whatever stream / device the tensors live on; `dist` = torch.distributed (None or
     world 1: all wraps are local)."""
     import torch
@@ -94,6 +95,62 @@ def exchange(tensors, n, rank, tiles, dist=None, h=HALO):
             v = t[r_hi]
             nb_ = v.numel() * v.element_size()
             v.copy_(in_hi[off_hi:off_hi + nb_].view(t.dtype).view(v.shape)); off_hi += nb_
+
+
+class Comm:
+    """The C++ side of the exchange (include/htr_b200.h: htr_comm_*, htr_halo_exchange; csrc/htr_halo.cuh): pack kernel,
+    ncclSend/ncclRecv inside one group, unpack kernel per phase, on the caller's stream.  torch.distributed is only used
+    once, to hand rank 0's 128-byte NCCL id to the other ranks."""
+
+    def __init__(self, solver, tiles, rank, world, dist=None):
+        import ctypes as C
+        import torch
+        self.C, self.L, self.torch = C, solver.L, torch
+        L = self.L
+        L.htr_comm_init.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.htr_halo_exchange.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.htr_allreduce_max.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.htr_comm_free.argtypes = [C.c_void_p]
+        idbuf = torch.zeros(128, dtype=torch.uint8)
+        if world > 1:
+            if rank == 0:
+                raw = (C.c_uint8 * 128)()
+                rc = L.htr_comm_get_unique_id(raw)
+                assert rc == 0, f"htr_comm_get_unique_id failed ({rc}): is libnccl.so.2 loadable?"
+                idbuf = torch.tensor(list(raw), dtype=torch.uint8)
+            idbuf = idbuf.cuda()
+            dist.broadcast(idbuf, 0)
+            idbuf = idbuf.cpu()
+        raw = (C.c_uint8 * 128)(*idbuf.tolist())
+        self.h = C.c_void_p()
+        rc = L.htr_comm_init(C.byref(self.h), raw, rank, world, tiles[0], tiles[1], tiles[2])
+        assert rc == 0, f"htr_comm_init failed ({rc})"
+
+    def exchange(self, fl, names, h=HALO):
+        """Ghost planes of the named fields of block `fl` from the neighbouring blocks (current stream)."""
+        from .core import Acc
+        C = self.C
+        st = fl.struct()
+        accs = (Acc * len(names))(*[getattr(st, n) for n in names])
+        cb = (C.c_int * len(names))(*[fl.t[n][0, 0, 0].numel() * fl.t[n].element_size() for n in names])
+        tile = fl.tile()
+        rc = self.L.htr_halo_exchange(self.h, len(names), accs, cb, C.byref(tile), h,
+                                      C.c_void_p(self.torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise RuntimeError(f"htr_halo_exchange failed with code {rc}")
+
+    def allreduce_max(self, t):
+        rc = self.L.htr_allreduce_max(self.h, self.C.c_void_p(t.data_ptr()), t.numel(),
+                                      self.C.c_void_p(self.torch.cuda.current_stream().cuda_stream))
+        if rc != 0:
+            raise RuntimeError(f"htr_allreduce_max failed with code {rc}")
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.L.htr_comm_free(self.h)
+        except Exception:
+            pass
 
 
 def shell_rects(origin, n, h=HALO):
@@ -147,6 +204,8 @@ class HaloExchanger:
         self.n = (fl.nx, fl.ny, fl.nz)
         assert fl.halos() == (HALO, HALO, HALO)
         self.comm = torch.cuda.Stream()
+        self.nccl = Comm(solver, self.tiles, rank, world, dist)
+        self._cfl = torch.zeros(1, dtype=torch.float64, device="cuda")
         self.ghost_boxes = [Rect.make(a, b) for a, b in shell_rects(fl.origin, self.n)]
         w = tuple(min(SHELL_W[d], max(HALO, self.n[d] // 4)) for d in range(3))
         inner, shells = boundary_rects(fl.origin, self.n, w)
@@ -157,7 +216,7 @@ class HaloExchanger:
     # ghost planes of the state, then ghost primitives/properties (on the current stream)
     def exchange_state(self):
         fl = self.fl
-        exchange([fl.t["Conserved"], fl.t["temperature"]], self.n, self.rank, self.tiles, self.dist)
+        self.nccl.exchange(fl, ["Conserved", "temperature"])
         for box in self.ghost_boxes:      # the owner's bits: T is the owner's converged value, no second Newton pass
             self.s.UpdateGhostPrimitiveFromConserved(fl, tile=box)
             self.s.UpdatePropertiesFromPrimitive(fl, tile=box)
@@ -166,7 +225,7 @@ class HaloExchanger:
         """Ghost planes of Conserved_old.  The multi-species positivity limiter of the TENO fluxes reads it at both
         cells of a face (src/prometeo_rhs.inl, partial densities after the stage), hence in the first ghost plane:
         call this whenever Conserved_old was set on the interior only.  initialize_temporaries() needs no message."""
-        exchange([self.fl.t["Conserved_old"]], self.n, self.rank, self.tiles, self.dist)
+        self.nccl.exchange(self.fl, ["Conserved_old"])
 
     def initialize_temporaries(self):
         """InitializeTemporaries (src/prometeo_rk.rg:46-56) over interior AND ghosts; the ghost planes of Conserved must
@@ -194,10 +253,10 @@ class HaloExchanger:
         fl, s = self.fl, self.s
         self.exchange_state()
         s.UpdateDucrosSensor(fl, vorticityScale, bounds=self.nowrap)
-        exchange([fl.t["DucrosSensor"]], self.n, self.rank, self.tiles, self.dist)
+        self.nccl.exchange(fl, ["DucrosSensor"])
         for d in range(3):
             s.UpdateShockSensor(fl, d, bounds=self.nowrap)
-        exchange([fl.t["shockSensorX"], fl.t["shockSensorY"], fl.t["shockSensorZ"]], self.n, self.rank, self.tiles, self.dist)
+        self.nccl.exchange(fl, ["shockSensorX", "shockSensorY", "shockSensorZ"])
 
     def _fluxes(self, box, scheme, diffusion, rk, dt):
         fl, s = self.fl, self.s
@@ -221,6 +280,13 @@ class HaloExchanger:
         main.wait_stream(self.comm)
         for box in self.shells:
             s.UpdateDerivatives(fl, scheme, diffusion, chemistry, rk, dt, tile=box, bounds=self.nowrap)
+
+    def max_spectral_radius(self):
+        """CalculateMaxSpectralRadius of the block followed by the MAX over all ranks (src/prometeo.rg:1161-1165): the
+        same time step on every rank."""
+        t = self.s.CalculateMaxSpectralRadius(self.fl, sync=False)
+        self.nccl.allreduce_max(t)
+        return float(t.item())
 
     def launches_per_step(self, diffusion, chemistry, scheme="Hybrid"):
         from .core import rhs_launches

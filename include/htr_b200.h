@@ -182,6 +182,25 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
                  const double *h_Conserved, const double *h_Conserved_old, double *h_temperature,
                  double *h_Conserved_t, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
 
+/* ---- multi-GPU: block decomposition and ghost-plane exchange (mirrors src/prometeo_partitioner.rg:436-446 tiling,
+ * :1107-1352 ghost partitions; Legion/Realm moves the ghosts implicitly in the reference) ----
+ * One process per GPU.  The global box is cut into tiles = [tx, ty, tz] equal blocks, rank = cx + tx*(cy + ty*cz), periodic
+ * neighbours.  htr_comm_get_unique_id on rank 0 returns 128 bytes that the caller distributes to all ranks (MPI, a file,
+ * torch.distributed ...); htr_comm_init is collective.  With one rank no NCCL is needed (all wraps are local copies). */
+typedef struct htr_comm_s htr_comm;
+int htr_comm_get_unique_id(void *id128);
+int htr_comm_init(htr_comm **comm, const void *id128, int rank, int nranks, int tx, int ty, int tz);
+int htr_comm_free(htr_comm *comm);
+int htr_comm_rank_of_tile(const htr_comm *comm, int cx, int cy, int cz);
+/* Fills the `halo` ghost planes per side of `nfields` fields of this rank's block (interior = `interior`, global
+ * coordinates; cellBytes[k] = bytes per cell of field k) from the neighbouring blocks: three phases x -> y -> z whose
+ * slabs include the ghosts of the earlier phases (edges and corners arrive without diagonal messages), per phase one
+ * pack kernel, ncclSend/ncclRecv to the +/- neighbours inside one group, one unpack kernel; all on `stream`. */
+int htr_halo_exchange(htr_comm *comm, int nfields, const htr_acc *fields, const int *cellBytes, const htr_rect *interior,
+                      int halo, void *stream);
+/* in-place MAX over all ranks of `count` device doubles (the spectral radius of the CFL condition, src/prometeo.rg:1161-1165) */
+int htr_allreduce_max(htr_comm *comm, double *d_values, int count, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
