@@ -37,6 +37,14 @@ for variant in ("strict", ""):
         for _ in range(2):
             ex.time_step(scheme, dt, True, chem, 1.0)
         torch.cuda.synchronize()
+        # the CFL reduction: every rank must end up with the same (global) spectral radius
+        sr = torch.tensor([ex.max_spectral_radius()], dtype=torch.float64, device="cuda")
+        allsr = [torch.zeros_like(sr) for _ in range(world)]
+        dist.all_gather(allsr, sr)
+        if rank == 0:
+            same_sr = all(float(a.item()) == float(sr.item()) for a in allsr)
+            print(f"{cfg['type']:12s} {variant or 'prod':6s} max spectral radius {float(sr.item()):.6e} identical on all ranks={same_sr}", flush=True)
+            ok = ok and same_sr
         got = fb.download(["Conserved", "temperature", "rho", "mu"])
         if rank == 0:
             # the whole box as one periodic tile; the stretched sizes need not be equal
