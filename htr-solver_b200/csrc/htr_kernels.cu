@@ -187,8 +187,10 @@ static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const 
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
    const int C[3] = {FB::X - (dir == 0), FB::Y - (dir == 1), FB::Z - (dir == 2)};
    const unsigned gx = (unsigned)((n[0] + C[0] - 1)/C[0]), gy = (unsigned)((n[1] + C[1] - 1)/C[1]), gz = (unsigned)((n[2] + C[2] - 1)/C[2]);
-   const uint64_t total = (uint64_t)gx*gy*gz, sms = (uint64_t)numSMs();
-   const unsigned grid = (unsigned)(total < sms ? total : sms);
+   int perSM = 1;          // resident CTAs of this instantiation (1 at 255 registers, 2-3 for the KG / diffusion forms)
+   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, masked_flux_kernel<dir, KIND, SCHEME>, FB::X*FB::Y*FB::Z, 0) != cudaSuccess || perSM < 1) perSM = 1;
+   const uint64_t total = (uint64_t)gx*gy*gz, slots = (uint64_t)numSMs()*(uint64_t)perSM;
+   const unsigned grid = (unsigned)(total < slots ? total : slots);
    dim3 block(FB::X, FB::Y, FB::Z);
    masked_flux_kernel<dir, KIND, SCHEME><<<grid, block, 0, st>>>(f, tile, B, ep, mask, flag, gx, gy, gz);
    return cudaGetLastError();
@@ -235,6 +237,9 @@ static int bulkEligible(std::initializer_list<std::pair<const racc*, int>> field
       const uintptr_t b = (uintptr_t)a.base;
       if (a.s[0] != 8*fc.second || (a.s[1] & 15) || (a.s[2] & 15) || (b & 7)) return 0;
       const int p = (int)((b >> 3) & 1);
+      // a field with an EVEN component count (e.g. MassFracs of the 4-species CH41StMix) has 16-byte cells: shifting the row start
+      // by one cell cannot repair a base that is 8 mod 16, so it must be aligned as it is
+      if ((fc.second & 1) == 0 && p != 0) return 0;
       if (parity < 0) parity = p; else if (p != parity) return 0;
    }
    return 1 | (parity << 1);

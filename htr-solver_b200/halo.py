@@ -243,6 +243,7 @@ class HaloExchanger:
         else:
             self.exchange_state()
         self.initialize_temporaries()
+        self._ghosts_current = True      # the ghosts hold the state stage 1 differentiates: its rhs() needs no second exchange
         for stage in (1, 2, 3):
             c1, c2, c3 = RK_C[stage - 1]
             self.rhs(scheme, diffusion, chemistry, (c1, c2), Integrator_deltaTime*c3)
@@ -272,9 +273,11 @@ class HaloExchanger:
         exactly one box and each box runs the reference's order (chem, Euler z,y,x, diffusion z,y,x)."""
         torch, fl, s = self.torch, self.fl, self.s
         main = torch.cuda.current_stream()
-        self.comm.wait_stream(main)
-        with torch.cuda.stream(self.comm):
-            self.exchange_state()
+        fresh, self._ghosts_current = getattr(self, "_ghosts_current", False), False
+        if not fresh:            # time_step: sensors() has just exchanged this very state for stage 1
+            self.comm.wait_stream(main)
+            with torch.cuda.stream(self.comm):
+                self.exchange_state()
         # each box is one htr_rhs call (0 + chem + Euler z,y,x + diffusion z,y,x over the box)
         s.UpdateDerivatives(fl, scheme, diffusion, chemistry, rk, dt, tile=self.inner, bounds=self.nowrap)
         main.wait_stream(self.comm)
