@@ -2,19 +2,33 @@
 // mechanics and htr_fast.cuh for the algorithm: same tiles, same arithmetic, same deferral rules as
 // fast::euler_xy_kernel -- only the way the tile reaches shared memory and its layout there differ).
 #pragma once
+#include <cuda.h>            // CUtensorMap (type only; the encoder is fetched with cudaGetDriverEntryPoint)
 #include "htr_fast.cuh"
 #include "htr_bulk.cuh"
 
 namespace htr {
 namespace fast {
 
+constexpr int pad16(int n) { return (n + 15)/16*16; }     // doubles: 128-byte sections (TMA tensor destinations)
 template<int TY> struct XYB {
    static constexpr int W = 38, ROWS = TY + 5, NC = W*ROWS, NT = 32*TY;
-   // tiles in doubles, each in the field's own [row][x][comp] order; H is derived after arrival
-   static constexpr int O_RHO = 0, O_P = NC, O_U = 2*NC, O_Y = 5*NC, O_H = (5 + nSpec)*NC, ND = (6 + nSpec)*NC;
+   // tiles in doubles, each in the field's own [row][x][comp] order (= one TMA box per field); H is derived after arrival
+   static constexpr int O_RHO = 0, O_P = pad16(NC), O_U = O_P + pad16(NC), O_Y = O_U + pad16(3*NC), O_H = O_Y + pad16(nSpec*NC),
+                        ND = O_H + pad16(NC);
    static constexpr uint32_t ROW_BYTES = 8u*W*(1 + 1 + 3 + nSpec);        // one row of the four copied fields
-   static constexpr size_t SMEM = 16 + sizeof(double)*ND + 2*NC + NT;
+   static constexpr size_t SMEM = 128 + sizeof(double)*ND + 2*NC + NT;     // mbarrier in the first 128 bytes
 };
+
+// Tensor maps of the four copied fields over the part of the allocation this call may read (host: makeTensorMaps in
+// htr_kernels.cu): field k is a 3-D tensor (ncomp*nx, ny, nz) of doubles whose element (0,0,0) is cell (x0, y0, z0)
+// (tile-relative); one cp.async.bulk.tensor per field moves the whole W x ROWS tile, AoS fields as a merged (comp, x)
+// inner dimension.
+struct XYMaps { CUtensorMap m[4]; int x0, y0, z0, ok; };
+
+__device__ __forceinline__ void tensorLoad3D(void *dst, const CUtensorMap *map, int c0, int c1, int c2, uint64_t *bar) {
+   asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+                :: "r"(bulk::sAddr(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bulk::sAddr(bar)) : "memory");
+}
 
 template<int dir, int NC>
 HTR_DEV void ldsPointRaw(KGPoint &c, const double *sRho, const double *sP, const double *sU, const double *sY, const double *sH, const int idx) {
@@ -28,12 +42,12 @@ HTR_DEV void ldsPointRaw(KGPoint &c, const double *sRho, const double *sP, const
    c.un = c.u[dir];
 }
 
-template<int dir, int NC>
+template<int dir, class T>
 HTR_DEV void kgStdFluxRaw(double *Flux, const double *d, const int i0, const int step) {
    using namespace fast;
    KGPoint c[6];
    HTR_UNROLL
-   for (int k = 0; k < 6; k++) ldsPointRaw<dir, NC>(c[k], d, d + NC, d + 2*NC, d + 5*NC, d + (5 + nSpec)*NC, i0 + k*step);
+   for (int k = 0; k < 6; k++) ldsPointRaw<dir, T::NC>(c[k], d + T::O_RHO, d + T::O_P, d + T::O_U, d + T::O_Y, d + T::O_H, i0 + k*step);
    double fl[nEq + 1];
    HTR_UNROLL
    for (int i = 0; i < nEq + 1; i++) fl[i] = 0.0;
@@ -61,12 +75,12 @@ HTR_DEV void kgStdFluxRaw(double *Flux, const double *d, const int i0, const int
 template<int TY, bool HYBRID>
 __global__ void __launch_bounds__(32*TY, HTR_K2_MINB)
 euler_xy_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__restrict__ mask, int *__restrict__ flag,
-                     const int bulkOK) {
+                     const int bulkOK, const __grid_constant__ XYMaps maps) {
    using T = XYB<TY>;
    constexpr int W = T::W, NC = T::NC, NT = T::NT, ROWS = T::ROWS;
-   extern __shared__ __align__(16) unsigned char smraw[];
+   extern __shared__ __align__(128) unsigned char smraw[];
    uint64_t *bar = reinterpret_cast<uint64_t*>(smraw);
-   double *d = reinterpret_cast<double*>(smraw + 16);
+   double *d = reinterpret_cast<double*>(smraw + 128);
    uint8_t *sSensX = reinterpret_cast<uint8_t*>(d + T::ND);
    uint8_t *sSensY = sSensX + NC;
    uint8_t *sFlag = sSensY + NC;
@@ -92,7 +106,21 @@ euler_xy_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__r
    __syncthreads();
 
    auto rowValid = [&](int rr) { const int y = cy0 - 2 + rr; return y >= tile.lo[1] - 3 && y <= tile.hi[1] + 3; };
-   if (useBulk) {
+   // one tensor copy per field when no needed row of the tile leaves the box in y (those tiles wrap row by row below);
+   // rows / columns outside the mapped region are zero-filled by the TMA unit and never read by an updated cell
+   const int yFirst = (cy0 - 2 > tile.lo[1] - 3) ? cy0 - 2 : tile.lo[1] - 3;
+   const int yLast = (cy0 - 2 + ROWS - 1 < tile.hi[1] + 3) ? cy0 - 2 + ROWS - 1 : tile.hi[1] + 3;
+   const bool useTensor = useBulk && maps.ok && yFirst >= B.lo[1] && yLast <= B.hi[1];
+   if (useTensor) {
+      if (tid == 0) {
+         bulk::mbarExpectTx(bar, (uint32_t)ROWS*T::ROW_BYTES);
+         const int cx = xs - maps.x0, cy = (cy0 - 2) - maps.y0, cz = c.z - maps.z0;
+         tensorLoad3D(d + T::O_RHO, &maps.m[0], cx, cy, cz, bar);
+         tensorLoad3D(d + T::O_P, &maps.m[1], cx, cy, cz, bar);
+         tensorLoad3D(d + T::O_U, &maps.m[2], 3*cx, cy, cz, bar);
+         tensorLoad3D(d + T::O_Y, &maps.m[3], nSpec*cx, cy, cz, bar);
+      }
+   } else if (useBulk) {
       if (j == 0) {                                          // warp 0 issues the copies
          if (i == 0) {
             int nv = 0;
@@ -167,7 +195,7 @@ euler_xy_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__r
       if (xAct) bad = ld<int>(f.nType_x, q) != Std_node;
       if (yAct) bad = bad || (ld<int>(f.nType_y, q) != Std_node);
    }
-   if (useBulk) bulk::mbarWait(bar, 0);
+   if (useBulk) bulk::mbarWait(bar, 0);       // tensor or row copies: same barrier phase
    else __syncthreads();
    HTR_UNROLL
    for (int k = 0; k < PER; k++) {
@@ -184,11 +212,11 @@ euler_xy_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__r
    if (!anyBad) {
       if (yAct) {
          hy = !HYBRID || (sSensY[own - W] && sSensY[own] && sSensY[own + W]);
-         if (hy) kgStdFluxRaw<1, NC>(Fy, d, own - 2*W, W);
+         if (hy) kgStdFluxRaw<1, T>(Fy, d, own - 2*W, W);
       }
       if (xAct) {
          hx = !HYBRID || (sSensX[own - 1] && sSensX[own] && sSensX[own + 1]);
-         if (hx) kgStdFluxRaw<0, NC>(Fx, d, own - 2, 1);
+         if (hx) kgStdFluxRaw<0, T>(Fx, d, own - 2, 1);
       }
    }
    double Fm[nEq];

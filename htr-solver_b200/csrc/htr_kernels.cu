@@ -245,6 +245,63 @@ static int bulkEligible(std::initializer_list<std::pair<const racc*, int>> field
    return 1 | (parity << 1);
 }
 
+// ---- TMA tensor maps of the Euler-xy kernel (htr_fast_bulk.cuh: XYMaps) ---------------------------------------------
+// cuTensorMapEncodeTiled is a driver entry point: fetched through the runtime so that the library does not link libcuda.
+static bool g_no_tensor = false;        // htr_set_option("tensor", 0): row-wise bulk copies instead of tensor-map copies
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encodeTiled() {
+   static EncodeTiledFn fn = nullptr;
+   static bool tried = false;
+   if (!tried) {
+      tried = true;
+      void *p = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+         fn = reinterpret_cast<EncodeTiledFn>(p);
+   }
+   return fn;
+}
+// Maps rho, pressure, velocity, MassFracs over the cells this call may read: [max(tile.lo-3, bounds.lo), min(tile.hi+3,
+// bounds.hi)] in x and y, the tile's planes in z.  Requires what bulkEligible already checked (x dense, y/z strides
+// multiples of 16 bytes, common 8-byte parity); the x origin is moved one cell down if that makes the base 16-byte aligned
+// (that cell is never part of a box).
+template<int TY>
+static void makeTensorMaps(const rfluid &rf, const rbox &rt, const rbox &rb, int bulkOK, fast::XYMaps &maps) {
+   using T = fast::XYB<TY>;
+   memset(&maps, 0, sizeof(maps));
+   EncodeTiledFn enc = encodeTiled();
+   if (!enc || !(bulkOK & 1) || g_no_tensor) return;
+   int lo[3], hi[3];
+   for (int d = 0; d < 2; d++) {
+      lo[d] = (-3 > rb.lo[d]) ? -3 : rb.lo[d];
+      hi[d] = (rt.hi[d] + 3 < rb.hi[d]) ? rt.hi[d] + 3 : rb.hi[d];
+   }
+   lo[2] = 0; hi[2] = rt.hi[2];
+   const racc *fld[4] = {&rf.rho, &rf.pressure, &rf.velocity, &rf.MassFracs};
+   const int nc[4] = {1, 1, 3, nSpec};
+   // common x origin: aligned for every field (odd component counts share the parity; even ones are aligned anywhere)
+   int x0 = lo[0];
+   for (int k = 0; k < 4; k++) {
+      const uintptr_t a = (uintptr_t)(fld[k]->base + (int64_t)lo[0]*fld[k]->s[0] + (int64_t)lo[1]*fld[k]->s[1]);
+      if (a & 15) { if (nc[k] & 1) x0 = lo[0] - 1; else return; }
+   }
+   for (int k = 0; k < 4; k++) {
+      const racc &a = *fld[k];
+      char *base = a.base + (int64_t)x0*a.s[0] + (int64_t)lo[1]*a.s[1];
+      if (((uintptr_t)base & 15) || (a.s[1] & 15) || (a.s[2] & 15) || a.s[0] != 8*nc[k]) return;
+      const cuuint64_t dims[3] = {(cuuint64_t)(hi[0] - x0 + 1)*nc[k], (cuuint64_t)(hi[1] - lo[1] + 1), (cuuint64_t)(hi[2] + 1)};
+      const cuuint64_t strides[2] = {(cuuint64_t)a.s[1], (cuuint64_t)a.s[2]};
+      const cuuint32_t box[3] = {(cuuint32_t)(T::W*nc[k]), (cuuint32_t)T::ROWS, 1};
+      const cuuint32_t es[3] = {1, 1, 1};
+      if (box[0] > 256 || dims[0] < 1 || dims[1] < 1) return;
+      if (enc(&maps.m[k], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, base, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return;
+   }
+   maps.x0 = x0; maps.y0 = lo[1]; maps.z0 = 0; maps.ok = 1;
+}
+
 enum { PART_EZ = 1, PART_EXY = 2, PART_DZ = 4, PART_DXY = 8, PART_ALL = 15 };
 
 template<int SCHEME>
@@ -275,7 +332,9 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
       dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TY - 2)/(TY - 1)), (unsigned)n[2]);
       dim3 block(32, TY, 1);
       const int bulkOK = bulkEligible({{&rf.rho, 1}, {&rf.pressure, 1}, {&rf.velocity, 3}, {&rf.MassFracs, nSpec}});
-      fast::euler_xy_bulk_kernel<TY, HY><<<grid, block, fast::XYB<TY>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 1, bulkOK);
+      fast::XYMaps maps;
+      makeTensorMaps<TY>(rf, rt, rb, bulkOK, maps);
+      fast::euler_xy_bulk_kernel<TY, HY><<<grid, block, fast::XYB<TY>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 1, bulkOK, maps);
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
@@ -919,6 +978,7 @@ int htr_set_option(const char *name, int value) {
    if (!name) return HTR_EINVAL;
    if (strcmp(name, "fast") == 0) { g_no_fast = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
+   if (strcmp(name, "tensor") == 0) { g_no_tensor = (value == 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
    if (strcmp(name, "march") == 0) { if (value < 0 || value > 7) return HTR_EINVAL; g_march = value; return HTR_OK; }
