@@ -77,6 +77,8 @@ def kernel_bytes(kind, nspec, scheme, diffusion=True):
         if diffusion:
             b += 8 * (3 + 3 * nspec + 6)
         return b
+    if kind == "diffusion_xyz":     # the fused three-direction kernel: state once, m_s x 3, m_d x 3, 3 nType; Conserved_t RMW
+        return 8 * (4 + 3 + 3 * nspec + 6) + 12 + 2 * 8 * neq
     if kind == "chem":
         return 8 * (3 + nspec) + 2 * 8 * nspec
     if kind == "zero":
@@ -383,7 +385,9 @@ def run_gpu(args, rank, world, local_rank):
         if staged and (march & 2):
             parts = [("euler_z_march", 1), ("plane_march", 2)]
         elif staged:
-            parts = [("euler_z_march" if march & 1 else "euler_z_chem", 1), ("euler_xy", 2)] + ([("diffusion_z", 4), ("diffusion_xy", 8)] if diffusion else [])
+            diff3 = any(kv.replace(" ", "") == "diff3=1" for kv in args.opt)          # library default: off
+            dparts = ([("diffusion_xyz", 8)] if diff3 else [("diffusion_z", 4), ("diffusion_xy", 8)]) if diffusion else []
+            parts = [("euler_z_march" if march & 1 else "euler_z_chem", 1), ("euler_xy", 2)] + dparts
         if staged:
             for label, m in parts:
                 timed(label, lambda m=m: solver.UpdateDerivativesParts(m, fl, scheme, diffusion, chemistry, (1.0, 0.0), 1e-3, tile=tile, bounds=bounds))

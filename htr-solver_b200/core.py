@@ -63,7 +63,7 @@ def rhs_launches(scheme, diffusion, chemistry, fast=True, march=True):
         # Euler-z march + its masked pass; plane march + masked Euler y, x (+ masked diffusion z, y, x)
         return 2 + 3 + (3 if diffusion else 0)
     if fast and scheme in ("Hybrid", "SkewSymmetric"):
-        return 5 + (5 if diffusion else 0)       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked
+        return 5 + (5 if diffusion else 0)       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked
     return 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
 
 

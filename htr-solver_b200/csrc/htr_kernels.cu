@@ -199,6 +199,11 @@ static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const 
 // Fast path of  Conserved_t = 0 (+chem) + Euler z,y,x  for the Hybrid and SkewSymmetric schemes
 // (htr_fast.cuh) followed by the masked generic kernels for the cells it deferred.
 // `scratch` holds two mask bytes per cell of the tile.
+// htr_set_option("diff3", 1): diffusion z, y, x in one pass (htr_march.cuh: diffusion3_staged_kernel) instead of the two staged
+// kernels.  Off by default: measured on B200 at 512^3 AirMix (profiles/r2_v8_*) 51.1 ms (45.6 ms at 2 CTAs per SM) against
+// 13.7 + 23.1 ms -- the operands of the planes p-1 / p+1 are read from global memory inside the flux phase (L2 hits, but
+// ~80 dependent, component-strided loads per cell on the critical path of every warp), which costs more than the pass it saves.
+static bool g_diff3 = false;
 static bool g_bulk_diffusion = false;   // htr_set_option("bulk_diffusion", 1): TMA bulk staging for the diffusion kernels too
 static bool g_no_pipe = false;          // htr_set_option("pipeline", 0): htr_host_rhs without the z-slab copy/compute overlap
 static bool g_no_bulk = false;          // htr_set_option("bulk", 0): cooperative loads instead of TMA bulk copies
@@ -358,6 +363,18 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       cudaFuncSetAttribute(fast::diffusion_bulk_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<1, TJ>::SMEM);
    }
    cudaError_t e;
+   if (g_diff3 && !g_bulk_diffusion) {
+      // all three directions in one pass over Conserved_t (htr_march.cuh: diffusion3_staged_kernel); PART_DXY stands for it
+      if (!(parts & PART_DXY)) return cudaSuccess;
+      if (firstUseOnDevice(6))
+         cudaFuncSetAttribute(march::diffusion3_staged_kernel<TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
+      dim3 g3((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
+      march::diffusion3_staged_kernel<TJ><<<g3, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
+      if ((e = cudaGetLastError()) != cudaSuccess) return e;
+      if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st);
+   }
    if (!g_bulk_diffusion) {
       // default: cooperative staging (htr_fast.cuh).  Measured on B200 (profiles/r1_v8_*): the bulk-copy variant below
       // needs ~90 row copies of 0.3-2.6 KB per CTA and is TMA-issue bound (Dz 3.2 vs 1.9 ms, Dxy 4.2 vs 3.3 ms at 256^3).
@@ -979,6 +996,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "fast") == 0) { g_no_fast = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
    if (strcmp(name, "tensor") == 0) { g_no_tensor = (value == 0); return HTR_OK; }
+   if (strcmp(name, "diff3") == 0) { g_diff3 = (value != 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
    if (strcmp(name, "march") == 0) { if (value < 0 || value > 7) return HTR_EINVAL; g_march = value; return HTR_OK; }

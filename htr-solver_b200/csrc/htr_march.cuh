@@ -702,5 +702,159 @@ plane_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ fla
    #undef HTR_ZP
 }
 
+
+// =============================================================================================
+// Conserved_t += diffusion z; += y; += x in ONE pass, without marching: the (x, y) tile of one plane is staged exactly
+// like fast::diffusion_staged_kernel<1> (same shared-memory layout, 3 CTAs per SM); the two z faces of a cell take the
+// operands of the planes p-1 and p+1 (own column only: 2 x 27 values + the velocity neighbours of the derivatives)
+// straight from global memory -- the CTAs of the neighbouring planes stage the same cells, so these are L2 hits, and
+// diffusion z no longer needs a pass of its own over the state and over Conserved_t (881 -> ~520 B/cell of DRAM traffic).
+// The price is one redundant face per cell (each z face is evaluated by both cells it separates).
+// Accumulation order per cell: += Dz, += Dy, += Dx (src/prometeo.rg:560-578).
+// =============================================================================================
+// x/y derivatives of the velocity at cell q (wrapped) read from global memory, as the z face wants them: dUdX dWdX dVdY dWdY
+HTR_DEV void zDerivsGlobal(double *g, const rfluid &f, const RPt &q, const rbox &B) {
+   RPt a = q, b = q;
+   a.x = fast::wrapCoord(q.x - 1, B.lo[0], B.hi[0]); b.x = fast::wrapCoord(q.x + 1, B.lo[0], B.hi[0]);
+   const double mx = ld<double>(f.dcsi_d, q);
+   g[0] = derivStd(ldc<double>(f.velocity, a, 0), ldc<double>(f.velocity, q, 0), ldc<double>(f.velocity, b, 0), mx);
+   g[1] = derivStd(ldc<double>(f.velocity, a, 2), ldc<double>(f.velocity, q, 2), ldc<double>(f.velocity, b, 2), mx);
+   a = q; b = q;
+   a.y = fast::wrapCoord(q.y - 1, B.lo[1], B.hi[1]); b.y = fast::wrapCoord(q.y + 1, B.lo[1], B.hi[1]);
+   const double my = ld<double>(f.deta_d, q);
+   g[2] = derivStd(ldc<double>(f.velocity, a, 1), ldc<double>(f.velocity, q, 1), ldc<double>(f.velocity, b, 1), my);
+   g[3] = derivStd(ldc<double>(f.velocity, a, 2), ldc<double>(f.velocity, q, 2), ldc<double>(f.velocity, b, 2), my);
+}
+// operand v (order of diffFaceStream) of cell q straight from global memory, loaded where it is used
+#define HTR_GOPS(q, g) [&](const int v) -> double { \
+   return v == 0 ? ld<double>(f.rho, q) : (v == 1 ? ld<double>(f.mu, q) : (v == 2 ? ld<double>(f.lam, q) : (v == 3 ? ld<double>(f.temperature, q) \
+        : (v < 7 ? ldc<double>(f.velocity, q, v - 4) : (v < DV_DI ? ldc<double>(f.MolarFracs, q, v - DV_X) : (v < DV_RY ? ldc<double>(f.Di, q, v - DV_DI) \
+        : (v < DV_G ? ldc<double>(f.Conserved, q, v - DV_RY) : (g)[v - DV_G]))))))); }
+
+template<int TJ>
+__global__ void __launch_bounds__(32*TJ, HTR_D_MINB)
+diffusion3_staged_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__restrict__ mask, int *__restrict__ flag) {
+   using T = fast::DTile<1, TJ>;
+   using L = fast::DLay<1>;
+   constexpr int W = T::W, NC = T::NC, NT = T::NT;
+   extern __shared__ double smem[];
+   double *s = smem;
+   static_assert(L::NVD*NC >= nEq*NT, "flux exchange reuses the staging buffer");
+
+   const int i = threadIdx.x, j = threadIdx.y;
+   const int tid = j*32 + i;
+   const int cx0 = tile.lo[0] - 1 + (int)blockIdx.x*31;
+   const int cy0 = tile.lo[1] - 1 + (int)blockIdx.y*(TJ - 1);
+   RPt c;
+   c.x = cx0 + i; c.y = cy0 + j; c.z = tile.lo[2] + blockIdx.z;
+   const bool inTile = c.x <= tile.hi[0] && c.y <= tile.hi[1];
+   const bool upd = inTile && j >= 1 && i >= 1;
+   bool bad = false;
+   for (int item = tid; item < 4*NC; item += NT) {
+      const int part = item/NC, n = item - part*NC;
+      const int rr = n/W, cc = n - rr*W;
+      const int x = cx0 + cc, y = cy0 + rr;
+      if (x <= tile.hi[0] + 1 && y <= tile.hi[1] + 1) {
+         const RPt q = {fast::wrapCoord(x, B.lo[0], B.hi[0]), fast::wrapCoord(y, B.lo[1], B.hi[1]), c.z};
+         bad = fast::stageDiffPart<1, NC>(part, s, n, f, q, B) || bad;
+      }
+   }
+   // own cell in the planes below and above (updated cells lie inside the tile: no wrap in x, y)
+   const RPt qm = {c.x, c.y, fast::wrapCoord(c.z - 1, B.lo[2], B.hi[2])}, qp = {c.x, c.y, fast::wrapCoord(c.z + 1, B.lo[2], B.hi[2])};
+   if (upd) {
+      // the z faces p-1/2 and p+1/2 are owned by the cells p-1 and p; the derivatives of p-1 and p+1 use their x / y node types
+      bad = bad || (ld<int>(f.nType_z, qm) != Std_node) || (ld<int>(f.nType_z, c) != Std_node) ||
+            (ld<int>(f.nType_x, qm) != Std_node) || (ld<int>(f.nType_y, qm) != Std_node) ||
+            (ld<int>(f.nType_x, qp) != Std_node) || (ld<int>(f.nType_y, qp) != Std_node);
+   }
+   const bool jAct = inTile && i >= 1, xAct = inTile && j >= 1;
+   RPt q = c;                                         // own cell, wrapped (it may be lo-1)
+   q.x = fast::wrapCoord(c.x, B.lo[0], B.hi[0]);
+   q.y = fast::wrapCoord(c.y, B.lo[1], B.hi[1]);
+   const bool anyBad = __syncthreads_or(bad);
+   const bool ok = !anyBad;
+   const int own = j*W + i;
+   // staged operand v of tile cell idx; the four derivative slots of a face come from `gexpr`
+   #define HTR_SOPS(idx, gexpr) [&](const int v) -> double { \
+      return v < 4 ? s[v*NC + (idx)] : (v < 7 ? s[(L::O_U + v - 4)*NC + (idx)] : (v < DV_DI ? s[(L::O_X + v - DV_X)*NC + (idx)] \
+           : (v < DV_RY ? s[(L::O_DI + v - DV_DI)*NC + (idx)] : (v < DV_G ? s[(L::O_RY + v - DV_RY)*NC + (idx)] : (gexpr))))); }
+   #define HTR_SG(idx, a, b, cc, d) s[(L::O_G + (v == DV_G ? (a) : (v == DV_G + 1 ? (b) : (v == DV_G + 2 ? (cc) : (d)))))*NC + (idx)]
+
+   double *Ct = at<double>(f.Conserved_t, c);
+   double ct[nEq], mz = 0.0, my = 0.0, mx = 0.0;
+   if (upd) {
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) ct[e] = Ct[e];
+      mz = ld<double>(f.dzet_d, c); my = ld<double>(f.deta_d, c); mx = ld<double>(f.dcsi_d, c);
+   }
+   // ---- z faces (both, from the planes below and above), applied first: += Dz ---------------------------------------
+   if (ok && upd) {
+      // z-face derivatives of the own cell in plane p: dUdX and dVdY are staged, dWdX and dWdY come from the staged velocity
+      double gC[4];
+      gC[0] = s[(L::O_G + 0)*NC + own];
+      gC[1] = derivStd(s[(L::O_U + 2)*NC + own - 1], s[(L::O_U + 2)*NC + own], s[(L::O_U + 2)*NC + own + 1], mx);
+      gC[2] = s[(L::O_G + 3)*NC + own];
+      gC[3] = derivStd(s[(L::O_U + 2)*NC + own - W], s[(L::O_U + 2)*NC + own], s[(L::O_U + 2)*NC + own + W], my);
+      double FzM[nEq], FzP[nEq], g[4];
+      zDerivsGlobal(g, f, qm, B);
+      diffFaceStream<2>(FzM, HTR_GOPS(qm, g), HTR_SOPS(own, gC[v - DV_G]), ld<double>(f.dzet_s, qm));
+      zDerivsGlobal(g, f, qp, B);
+      diffFaceStream<2>(FzP, HTR_SOPS(own, gC[v - DV_G]), HTR_GOPS(qp, g), ld<double>(f.dzet_s, c));
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) ct[e] += mz*(FzP[e] - FzM[e]);
+   }
+   // ---- y and x faces of the plane ----------------------------------------------------------------------------------------
+   double FJ[nEq], Fx[nEq];
+   HTR_UNROLL
+   for (int e = 0; e < nEq; e++) { FJ[e] = 0.0; Fx[e] = 0.0; }
+   if (ok && jAct) diffFaceStream<1>(FJ, HTR_SOPS(own, HTR_SG(own, 0, 1, 5, 6)), HTR_SOPS(own + W, HTR_SG(own + W, 0, 1, 5, 6)), ld<double>(f.deta_s, q));
+   if (ok && xAct) diffFaceStream<0>(Fx, HTR_SOPS(own, HTR_SG(own, 3, 2, 4, 6)), HTR_SOPS(own + 1, HTR_SG(own + 1, 3, 2, 4, 6)), ld<double>(f.dcsi_s, q));
+   #undef HTR_SOPS
+   #undef HTR_SG
+   double Fm[nEq];
+   HTR_UNROLL
+   for (int e = 0; e < nEq; e++) Fm[e] = __shfl_up_sync(0xffffffffu, Fx[e], 1);
+   __syncthreads();
+   double *sF = smem;
+   HTR_UNROLL
+   for (int e = 0; e < nEq; e++) sF[e*NT + tid] = FJ[e];
+   __syncthreads();
+   if (upd) {
+      if (ok) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) {
+            double v = ct[e];
+            v += my*(FJ[e] - sF[e*NT + tid - 32]);
+            v += mx*(Fx[e] - Fm[e]);
+            ct[e] = v;
+         }
+      }
+      mask[fast::maskIndex(c, tile)] = !ok;
+      if (!ok) *flag = 1;
+   }
+   // rows of Conserved_t leave through shared memory as contiguous spans (a deferred tile rewrites its old values)
+   if (f.Conserved_t.s[0] == 8*nEq) {
+      __syncthreads();
+      double *sOut = smem + j*(nEq*32);
+      if (upd) {
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) sOut[(i - 1)*nEq + e] = ct[e];
+      }
+      __syncwarp();
+      if (j >= 1 && c.y <= tile.hi[1]) {
+         RPt r0 = c; r0.x = cx0 + 1;
+         const int left = tile.hi[0] - r0.x + 1;
+         const int nval = nEq*(int)(left < 31 ? left : 31);
+         double *row = at<double>(f.Conserved_t, r0);
+         HTR_UNROLL
+         for (int e = 0; e < nEq; e++) { const int m = e*32 + i; if (m < nval) row[m] = sOut[m]; }
+      }
+   } else if (upd && ok) {
+      HTR_UNROLL
+      for (int e = 0; e < nEq; e++) Ct[e] = ct[e];
+   }
+}
+#undef HTR_GOPS
+
 } // namespace march
 } // namespace htr
