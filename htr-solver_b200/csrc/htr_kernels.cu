@@ -180,8 +180,85 @@ static bool firstUseOnDevice(int slot) {
    return true;
 }
 
+// ---- deferred cells as a compacted list --------------------------------------------------------------------------
+// The block scan (masked_flux_kernel) evaluates a 255-register TENO face for every lane of a block that holds one flagged
+// cell; flagged cells of a shock or a front form thin sheets, so most of those lanes idle (air256_front: 13 of 21.7 ms for
+// 1.8 % of the cells).  Instead the mask is compacted once into a list of cell indices and one thread takes one flagged
+// cell: both its faces, then the reference's  Conserved_t[p] += m[p]*(F[p+1/2] - F[p-1/2]).  Same face functions, same bits.
+__global__ void __launch_bounds__(256) compact_mask_kernel(const uint8_t *__restrict__ mask, const int64_t cells, const int *__restrict__ flag,
+                                                           int *__restrict__ list, int *__restrict__ count) {
+   if (*flag == 0) return;
+   const int lane = threadIdx.x & 31;
+   for (int64_t base = ((int64_t)blockIdx.x*blockDim.x + threadIdx.x) - lane; base < cells; base += (int64_t)gridDim.x*blockDim.x) {
+      const int64_t c = base + lane;
+      const bool on = c < cells && mask[c] != 0;
+      const unsigned b = __ballot_sync(0xffffffffu, on);
+      if (b == 0) continue;
+      int pos = 0;
+      if (lane == 0) pos = atomicAdd(count, __popc(b));
+      pos = __shfl_sync(0xffffffffu, pos, 0);
+      if (on) list[pos + __popc(b & ((1u << lane) - 1))] = (int)c;
+   }
+}
+
+template<int dir, int KIND, int SCHEME>
+__global__ void __launch_bounds__(128)
+listed_flux_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep,
+                   const int *__restrict__ list, const int *__restrict__ count) {
+   const int n = *count;
+   const int64_t nx = tile.hi[0] - tile.lo[0] + 1, ny = tile.hi[1] - tile.lo[1] + 1;
+   for (int t = blockIdx.x*blockDim.x + threadIdx.x; t < n; t += gridDim.x*blockDim.x) {
+      const int64_t idx = list[t];
+      Pt c;
+      c.x = tile.lo[0] + idx % nx; c.y = tile.lo[1] + (idx/nx) % ny; c.z = tile.lo[2] + idx/(nx*ny);
+      const int tc = ld<int>(nTypeOf<dir>(f), c);
+      const Pt pm = shift<dir>(c, offM1(tc), B);             // owner of the cell's minus face (fluxBlock: fd == 0)
+      const int64_t cd = (dir == 0) ? c.x : ((dir == 1) ? c.y : c.z);
+      double Fp[nEq], Fm[nEq];
+      if (KIND == FLUX_EULER) {
+         eulerFace<dir, SCHEME>(Fm, f, pm, ld<int>(nTypeOf<dir>(f), pm), B, ep);
+         eulerFace<dir, SCHEME>(Fp, f, c, tc, B, ep);
+      } else {
+         // the face below the tile's second cell is the span's first plus face (htr_diffusion.cuh: spanFirst)
+         diffusionFaceFlux<dir>(Fm, f, pm, B, cd == tile.lo[dir] + 1);
+         diffusionFaceFlux<dir>(Fp, f, c, B, cd == tile.lo[dir]);
+      }
+      const double m = ld<double>((KIND == FLUX_EULER) ? m_eOf<dir>(f) : m_dOf<dir>(f), c);
+      double *Ct = at<double>(f.Conserved_t, c);
+      HTR_UNROLL
+      for (int i = 0; i < nEq; i++) Ct[i] += m*(Fp[i] - Fm[i]);
+   }
+}
+
+template<int dir, int KIND, int SCHEME>
+static cudaError_t launchMaskedScan(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
+                                     const uint8_t *mask, const int *flag, cudaStream_t st);
+static thread_local int *g_list = nullptr;      // list + counter of the running htr_rhs call (library scratch), or null
+static bool g_no_list = false;                  // htr_set_option("list", 0): the block scan (masked_flux_kernel) instead
+
+// `fresh`: the mask was (re)written since the last compaction; false = same mask as the previous call, reuse its list
 template<int dir, int KIND, int SCHEME>
 static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
+                                     const uint8_t *mask, const int *flag, cudaStream_t st, bool fresh = true) {
+   const int64_t cells = (tile.hi[0] - tile.lo[0] + 1)*(tile.hi[1] - tile.lo[1] + 1)*(tile.hi[2] - tile.lo[2] + 1);
+   if (g_list && !g_no_list && cells < ((int64_t)1 << 31)) {
+      int *count = g_list, *list = g_list + 4;
+      if (fresh) {
+         cudaError_t e = cudaMemsetAsync(count, 0, sizeof(int), st);
+         if (e != cudaSuccess) return e;
+         const int64_t g = (cells + 255)/256;
+         compact_mask_kernel<<<(unsigned)(g < (int64_t)numSMs()*8 ? g : (int64_t)numSMs()*8), 256, 0, st>>>(mask, cells, flag, list, count);
+      }
+      int perSM = 1;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, listed_flux_kernel<dir, KIND, SCHEME>, 128, 0) != cudaSuccess || perSM < 1) perSM = 1;
+      listed_flux_kernel<dir, KIND, SCHEME><<<(unsigned)(numSMs()*perSM), 128, 0, st>>>(f, tile, B, ep, list, count);
+      return cudaGetLastError();
+   }
+   return launchMaskedScan<dir, KIND, SCHEME>(f, tile, B, ep, mask, flag, st);
+}
+
+template<int dir, int KIND, int SCHEME>
+static cudaError_t launchMaskedScan(const htr_fluid &f, const htr_rect &tile, const htr_rect &B, const EulerParams &ep,
                                      const uint8_t *mask, const int *flag, cudaStream_t st) {
    using FB = FaceBlock<dir>;
    const int64_t n[3] = {tile.hi[0] - tile.lo[0] + 1, tile.hi[1] - tile.lo[1] + 1, tile.hi[2] - tile.lo[2] + 1};
@@ -343,7 +420,7 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
       cudaError_t e = cudaGetLastError();
       if (e != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
-      if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskXY, flags + 1, st, false)) != cudaSuccess) return e;
    }
    return cudaSuccess;
 }
@@ -372,8 +449,8 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       march::diffusion3_staged_kernel<TJ><<<g3, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
-      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
-      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st);
+      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false)) != cudaSuccess) return e;
+      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false);
    }
    if (!g_bulk_diffusion) {
       // default: cooperative staging (htr_fast.cuh).  Measured on B200 (profiles/r1_v8_*): the bulk-copy variant below
@@ -393,7 +470,7 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
-      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st);
+      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false);
    }
    const int bulkOK = bulkEligible({{&rf.rho, 1}, {&rf.mu, 1}, {&rf.lam, 1}, {&rf.temperature, 1}, {&rf.MolarFracs, nSpec},
                                     {&rf.Di, nSpec}, {&rf.Conserved, nEq}, {&rf.velocity, 3}});
@@ -408,7 +485,7 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       fast::diffusion_bulk_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DB<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3, bulkOK);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
-      if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false)) != cudaSuccess) return e;
    }
    return cudaSuccess;
 }
@@ -509,12 +586,12 @@ static cudaError_t launchMarch(bool chem, bool diffusion, const htr_fluid &f, co
       else           march::plane_march_kernel<HY, false><<<grid, block, march::PLay<false>::SMEM, st>>>(u, maskP, flags + 1, kch);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st)) != cudaSuccess) return e;
-      if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st)) != cudaSuccess) return e;
+      if ((e = launchMasked<0, FLUX_EULER, SCHEME>(f, tile, B, ep, maskP, flags + 1, st, false)) != cudaSuccess) return e;
       if (diffusion) {
          const EulerParams e0 = {0, 0, 0};
-         if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st)) != cudaSuccess) return e;
-         if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st)) != cudaSuccess) return e;
-         if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st)) != cudaSuccess) return e;
+         if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st, false)) != cudaSuccess) return e;
+         if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st, false)) != cudaSuccess) return e;
+         if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, e0, maskP, flags + 1, st, false)) != cudaSuccess) return e;
       }
    }
    return cudaSuccess;
@@ -996,6 +1073,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "fast") == 0) { g_no_fast = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk") == 0) { g_no_bulk = (value == 0); return HTR_OK; }
    if (strcmp(name, "tensor") == 0) { g_no_tensor = (value == 0); return HTR_OK; }
+   if (strcmp(name, "list") == 0) { g_no_list = (value == 0); return HTR_OK; }
    if (strcmp(name, "diff3") == 0) { g_diff3 = (value != 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
@@ -1323,8 +1401,11 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
    rfluid rf; rbox rt, rb;
    if ((scheme == HTR_SCHEME_HYBRID || scheme == HTR_SCHEME_SKEWSYMMETRIC) && !g_no_fast && makeRelative(*f, *tile, *bounds, rf, rt, rb)) {
       const int64_t cells = (tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
-      uint8_t *scratch = (uint8_t*)scratchFor((size_t)(2*cells + 16), st);
+      // 16 bytes of flags, two mask bytes per cell, then (16-byte aligned) the counter and the list of deferred cells
+      const size_t listOff = ((size_t)(2*cells + 16) + 15)/16*16;
+      uint8_t *scratch = (uint8_t*)scratchFor(listOff + 16 + 4*(size_t)cells, st);
       if (!scratch) return 1000 + (int)cudaErrorMemoryAllocation;
+      struct ListScope { ListScope(int *p) { g_list = p; } ~ListScope() { g_list = nullptr; } } listScope(reinterpret_cast<int*>(scratch + listOff));
       const EulerParams ep = {RK0, RK1, deltaTime};
       march::UF u;
       if (g_march && makeUniform(rf, rt, rb, scheme == HTR_SCHEME_HYBRID, chemistry != 0, diffusion != 0, u)) {

@@ -350,10 +350,13 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         # csrc/htr_fast.cuh ("march" = 0); 3: the default (Euler-z march + three staged kernels); 0: the per-task kernels
         # 4: Euler-z march + plane march without its diffusion phase + staged diffusion ("march" = 5)
         # 5: the default with the fused three-direction diffusion kernel ("diff3" = 1) instead of the two staged ones
-        for path, (fast, march, diff3) in {1: (1, 3, 0), 2: (1, 0, 0), 3: (1, 1, 0), 4: (1, 5, 0), 5: (1, 1, 1), 0: (0, 0, 0)}.items():
+        # 6: the default with the deferred cells found by the block scan ("list" = 0) instead of the compacted list
+        for path, (fast, march, diff3, lst) in {1: (1, 3, 0, 1), 2: (1, 0, 0, 1), 3: (1, 1, 0, 1), 4: (1, 5, 0, 1), 5: (1, 1, 1, 1),
+                                                6: (1, 1, 0, 0), 0: (0, 0, 0, 1)}.items():
             s.set_option("fast", fast)
             s.set_option("march", march)
             s.set_option("diff3", diff3)
+            s.set_option("list", lst)
             fl.t["Conserved_t"].fill_(-3.0)
             s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=(0.75, 0.25), deltaTime=1e-3)
             out[path] = fl.download(["Conserved_t"])["Conserved_t"]
@@ -361,6 +364,7 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         s.set_option("fast", 1)
         s.set_option("march", 1)
         s.set_option("diff3", 0)
+        s.set_option("list", 1)
     o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=0.75, RK1=0.25, dt=1e-3)
     scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
     if chem:
@@ -370,10 +374,10 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
         f["Conserved_t"][...] = ref
     if variant == "strict":
-        for k in (1, 2, 3, 4, 5):
+        for k in (1, 2, 3, 4, 5, 6):
             assert np.array_equal(out[k], out[0]), k
     else:
-        for k in (1, 2, 3, 4, 5):
+        for k in (1, 2, 3, 4, 5, 6):
             assert scaled_err(out[k], out[0], scale) <= TOL_FLUX, k
     assert scaled_err(out[1], f["Conserved_t"], scale) <= (TOL_CHEM if chem else TOL_FLUX)
 
