@@ -14,6 +14,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
+HTR_ETOOBIG = -4        # include/htr_b200.h
 SCHEMES = {"Hybrid": 0, "TENO": 1, "TENOA": 2, "TENOLAD": 3, "SkewSymmetric": 4}
 
 # (name, components: 0 scalar, 'S' nSpec, 'E' nEq, 3 vec3, numpy dtype) -- order of htr_fluid
@@ -114,6 +115,9 @@ def load_library(mix, variant=""):
     L.htr_time_step.argtypes = [i, i, i, i, d, vp, vp, vp, d, vp]
     L.htr_rhs.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
     L.htr_rhs_parts.argtypes = [i, i, i, i, vp, vp, vp, d, d, d, vp]
+    L.htr_rhs_no_alloc.argtypes = [i, i, i, vp, vp, vp, d, d, d, vp]
+    L.htr_rhs_no_alloc_max_cells.restype = C.c_int64
+    L.htr_rhs_no_alloc_max_cells.argtypes = []
     L.htr_host_rhs.argtypes = [i, i, i, i, d, vp, vp, vp, vp, vp, vp, vp, d, d, d, vp]
     L.htr_probe_fp64.argtypes = [d, vp, vp]
     L.htr_chemistry_failures_on.argtypes = [vp]
@@ -344,6 +348,17 @@ class Solver:
         t, b = self._rects(fl, tile, bounds)
         self._check(self.L.htr_rhs(SCHEMES[scheme], int(diffusion), int(chemistry), C.byref(fl.struct()), t, b,
                                    RK_coeffs[0], RK_coeffs[1], deltaTime, self._stream()), "htr_rhs")
+
+    def UpdateDerivativesNoAlloc(self, fl, scheme, diffusion=True, chemistry=False, RK_coeffs=(1.0, 0.0), deltaTime=0.0,
+                                 tile=None, bounds=None):
+        """UpdateDerivatives through htr_rhs_no_alloc: scratch in the library's static device array (tiles of at most
+        htr_rhs_no_alloc_max_cells() cells), no allocation.  Returns the C return code instead of raising on HTR_ETOOBIG."""
+        t, b = self._rects(fl, tile, bounds)
+        rc = self.L.htr_rhs_no_alloc(SCHEMES[scheme], int(diffusion), int(chemistry), C.byref(fl.struct()), t, b,
+                                     RK_coeffs[0], RK_coeffs[1], deltaTime, self._stream())
+        if rc != HTR_ETOOBIG:
+            self._check(rc, "htr_rhs_no_alloc")
+        return rc
 
     def UpdateDerivativesParts(self, parts, fl, scheme, diffusion=True, chemistry=False, RK_coeffs=(1.0, 0.0), deltaTime=0.0,
                                tile=None, bounds=None):

@@ -1446,6 +1446,69 @@ int htr_rhs_parts(int parts, int scheme, int diffusion, int chemistry, const htr
    return rc;
 }
 
+// ---- htr_rhs without any allocation (no counterpart in the reference) ----
+// Callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it) get the staged
+// htr_rhs with its scratch (16 flag bytes, two mask bytes per cell, the counter and the list of deferred cells: 6 bytes per
+// cell + 48) in a file-scope device array instead of the cudaMalloc'ed, per-stream buffers of scratchFor().  Every GPU that
+// loads the library holds the array until exit; every call on a device shares it, so calls that overlap on the GPU (two
+// streams) race.  Nothing in it has to survive a call or start at zero: the flags and the list counter are cleared on the
+// stream by the launchers, every mask byte of the tile is written by the staged kernels before it is read.
+constexpr int64_t HTR_NOALLOC_MAX_CELLS = (int64_t)128*128*128;
+constexpr size_t HTR_NOALLOC_BYTES = 6*(size_t)HTR_NOALLOC_MAX_CELLS + 64;        // 12 MiB + 64 B
+static __device__ __align__(256) unsigned char g_noalloc_scratch[HTR_NOALLOC_BYTES];
+// the array's name is a host-side stand-in in host code: the device address is fetched once per device
+static uint8_t *g_noalloc_ptr[HTR_MAX_DEVICES] = {};
+
+int64_t htr_rhs_no_alloc_max_cells(void) { return HTR_NOALLOC_MAX_CELLS; }
+
+int htr_rhs_no_alloc(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
+                     const htr_rect *bounds, double RK0, double RK1, double deltaTime, void *stream) {
+   HTR_CHECK_COMMON(f, tile)
+   if (!bounds) return HTR_EINVAL;
+   if (scheme < 0 || scheme > HTR_SCHEME_SKEWSYMMETRIC) return HTR_EINVAL;
+   cudaStream_t st = (cudaStream_t)stream;
+   const int64_t cells = (tile->hi[0] - tile->lo[0] + 1)*(tile->hi[1] - tile->lo[1] + 1)*(tile->hi[2] - tile->lo[2] + 1);
+   if (cells > HTR_NOALLOC_MAX_CELLS) {
+      fprintf(stderr, "htr_rhs_no_alloc: tile of %lld cells exceeds the static scratch (at most %lld cells, 128^3); use htr_rhs\n",
+              (long long)cells, (long long)HTR_NOALLOC_MAX_CELLS);
+      return HTR_ETOOBIG;
+   }
+   rfluid rf; rbox rt, rb;
+   // the per-task sequence of htr_rhs (other schemes, "fast" = 0, strides beyond 32 bits) uses no scratch at all
+   if (!((scheme == HTR_SCHEME_HYBRID || scheme == HTR_SCHEME_SKEWSYMMETRIC) && !g_no_fast && makeRelative(*f, *tile, *bounds, rf, rt, rb)))
+      return htr_rhs_parts(PART_ALL, scheme, diffusion, chemistry, f, tile, bounds, RK0, RK1, deltaTime, stream);
+   const int dev = curDev();
+   if (!g_noalloc_ptr[dev]) {
+      void *p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);      // with this device current
+      if (e != cudaSuccess || !p) return cuerr(e != cudaSuccess ? e : cudaErrorInvalidSymbol);
+      g_noalloc_ptr[dev] = static_cast<uint8_t*>(p);
+   }
+   uint8_t *scratch = g_noalloc_ptr[dev];
+   const size_t listOff = ((size_t)(2*cells + 16) + 15)/16*16;
+   struct ListScope { ListScope(int *p) { g_list = p; } ~ListScope() { g_list = nullptr; } } listScope(reinterpret_cast<int*>(scratch + listOff));
+   const EulerParams ep = {RK0, RK1, deltaTime};
+   int parts = PART_ALL;
+   march::UF u;
+   if (g_march && makeUniform(rf, rt, rb, scheme == HTR_SCHEME_HYBRID, chemistry != 0, diffusion != 0, u)) {
+      const bool planeAll = (g_march & 2) != 0, planeEuler = !planeAll && (g_march & 4) != 0;
+      const int mparts = (planeAll || planeEuler) ? (PART_EZ | PART_EXY) : PART_EZ;
+      const bool mdiff = diffusion != 0 && planeAll;
+      const cudaError_t em = (scheme == HTR_SCHEME_HYBRID)
+         ? launchMarch<HTR_SCHEME_HYBRID>(chemistry != 0, mdiff, *f, *tile, *bounds, u, ep, scratch, st, mparts)
+         : launchMarch<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, mdiff, *f, *tile, *bounds, u, ep, scratch, st, mparts);
+      if (em != cudaSuccess || planeAll) return cuerr(em);
+      if (planeEuler) return diffusion ? cuerr(launchFastDiffusion(*f, *tile, *bounds, rf, rt, rb, scratch, st, parts)) : HTR_OK;
+      parts &= ~PART_EZ;
+   }
+   cudaError_t e = (scheme == HTR_SCHEME_HYBRID)
+      ? launchFastEuler<HTR_SCHEME_HYBRID>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts)
+      : launchFastEuler<HTR_SCHEME_SKEWSYMMETRIC>(chemistry != 0, *f, *tile, *bounds, rf, rt, rb, ep, scratch, st, parts);
+   if (e != cudaSuccess) return cuerr(e);
+   if (diffusion && (e = launchFastDiffusion(*f, *tile, *bounds, rf, rt, rb, scratch, st, parts)) != cudaSuccess) return cuerr(e);
+   return HTR_OK;
+}
+
 // ---- one RK3 time step of a block without boundary nodes (MainLoopBody, src/prometeo.rg:1348-1470) ---------------
 // shock sensors once (Hybrid only, src/prometeo_sensor.rg:104-122); with implicit chemistry the operator-split
 // half step (:1360-1395: UpdateDerivatives(RK_coeffs = (0, 1), dt/2) without chemistry sources, UpdateChemistry(dt),

@@ -29,6 +29,7 @@ extern "C" {
 #define HTR_EINVAL (-1)   /* bad argument (direction, scheme, empty accessor that the task reads) */
 #define HTR_ENOMIX (-2)   /* mixture not loaded: call htr_set_mixture first (LoadMixtureTask, src/prometeo_mixture.cu:35-47) */
 #define HTR_EMIXTYPE (-3) /* constructor for another mixture than the one this library was built for */
+#define HTR_ETOOBIG (-4)  /* htr_rhs_no_alloc: the tile has more cells than the library's static scratch holds */
 
 /* Affine accessor: address(p) = base + p.x*stride[0] + p.y*stride[1] + p.z*stride[2], p in GLOBAL
  * grid coordinates, strides in BYTES (replaces FieldAccessor<...,Realm::AffineAccessor<T,3,coord_t>>,
@@ -152,6 +153,19 @@ int htr_max_spectral_radius(const htr_fluid *f, const htr_rect *tile, double *d_
  * + Euler z,y,x + diffusion z,y,x, in the reference's accumulation order. */
 int htr_rhs(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
             const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+
+/* htr_rhs for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * NO COUNTERPART IN THE REFERENCE.  Same arguments, same kernels and same
+ * result as htr_rhs; the scratch of the staged path (deferral flags, two mask bytes per cell, the list of deferred cells:
+ * 6 bytes per cell) lives in a file-scope `static __device__` array of 12 MiB that every GPU loading the library holds until
+ * exit, instead of the cudaMalloc'ed per-stream buffers htr_rhs grows on demand.  Calls no cudaMalloc / cudaFree / allocating
+ * routine.  Limit: tiles of at most htr_rhs_no_alloc_max_cells() = 128^3 = 2 097 152 cells; a larger tile is rejected with
+ * HTR_ETOOBIG (and a line on stderr) before anything is launched.  All calls on one device share the array: calls that
+ * overlap on the GPU (different streams, no ordering between them) race; calls ordered on one stream are safe.  The array
+ * keeps the last call's contents; the entry point clears what must start at zero itself (flags, list counter). */
+int htr_rhs_no_alloc(int scheme, int diffusion, int chemistry, const htr_fluid *f, const htr_rect *tile,
+                     const htr_rect *bounds, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
+int64_t htr_rhs_no_alloc_max_cells(void);
 
 /* The same pass restricted to some of its staged kernels (timing / profiling only: a partial pass leaves
  * Conserved_t incomplete).  parts = bit mask: 1 Conserved_t = 0 + chem + Euler z; 2 += Euler y, x; 4 += diffusion z;
