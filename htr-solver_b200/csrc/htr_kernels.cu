@@ -1712,5 +1712,8 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
 
 } // extern "C"
 
+// non-periodic boundaries: NSCBC right-hand-side tasks and boundary-cell primitive updates (htr_nscbc_*, htr_set_*_bc)
+#include "htr_nscbc.cuh"
+
 // ghost-plane exchange over NCCL + scalar max-reduction (htr_comm_*, htr_halo_exchange, htr_allreduce_max)
 #include "htr_halo.cuh"

@@ -19,6 +19,7 @@ using namespace Legion;
 #include "prometeo_chem.hpp"
 #include "prometeo_variables.hpp"
 #include "prometeo_cfl.hpp"
+#include "prometeo_bc.hpp"
 #include "htr_b200.h"
 
 namespace {
@@ -322,6 +323,153 @@ DeferredValue<double> CalculateMaxSpectralRadiusTask::gpu_base_impl(const Args &
    return r;
 }
 
+// ---- non-periodic boundaries: NSCBC right-hand-side tasks (src/prometeo_rhs.cu:625-1560) -------------------------
+// Region order as in the reference's bodies: the written region (last) is the plane of boundary cells; the fields read at
+// the interior neighbour come with the Fluid / ghost regions in front of it.
+namespace {
+htr_bc_fields emptyBC() { htr_bc_fields b; memset(&b, 0, sizeof(b)); return b; }
+void flattenShock(const IncomingShockParams &P, double *q) {      // include/htr_b200.h: params of htr_nscbc_incoming_shock
+   q[0] = P.iShock;
+   for (int s = 0; s < nSpec; s++) q[1 + s] = P.MolarFracs[s];
+   double *r = q + 1 + nSpec;
+   r[0] = P.pressure0; r[1] = P.temperature0; for (int i = 0; i < 3; i++) r[2 + i] = P.velocity0[i];
+   r[5] = P.pressure1; r[6] = P.temperature1; for (int i = 0; i < 3; i++) r[7 + i] = P.velocity1[i];
+}
+template<direction dir, class Args>
+void nscbcInflow(int side, const Args &args, Regions &regions, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 3);
+   const Unpacker u(regions, 2, ctx, runtime);
+   const DirFields &D = DIR[dirIndex(dir)];
+   htr_fluid f = emptyFluid();
+   htr_bc_fields b = emptyBC();
+   f.MassFracs = u.ro<VecNSp>(0, FID_MassFracs); f.pressure = u.ro<double>(0, FID_pressure); f.velocity = u.ro<Vec3>(0, FID_velocity);
+   f.*D.nType = u.ro<int>(1, D.fNType); f.*D.m_d = u.ro<double>(1, D.fMd);
+   f.rho = u.ro<double>(1, FID_rho); f.SoS = u.ro<double>(1, FID_SoS); f.temperature = u.ro<double>(1, FID_temperature);
+   b.dudtBoundary = u.ro<Vec3>(1, FID_dudtBoundary); b.dTdtBoundary = u.ro<double>(1, FID_dTdtBoundary);
+   f.Conserved_t = u.rw<VecNEq>(2, FID_Conserved_t);
+   loadMix(args.mix);
+   const htr_rect bc = toRect(u.tile);
+   ok(htr_nscbc_inflow(dirIndex(dir), side, &f, &b, &bc, taskStream()));
+}
+template<direction dir, class Args>
+void nscbcOutflow(int side, const Args &args, Regions &regions, const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 4 && futures.size() == 1);
+   const Unpacker u(regions, 3, ctx, runtime);
+   htr_fluid f = emptyFluid();
+   f.velocity = u.ro<Vec3>(0, FID_velocity);
+   for (int d = 0; d < 3; d++) { f.*DIR[d].nType = u.ro<int>(1, DIR[d].fNType); f.*DIR[d].m_d = u.ro<double>(1, DIR[d].fMd); }
+   f.rho = u.ro<double>(1, FID_rho); f.mu = u.ro<double>(1, FID_mu);
+   f.MassFracs = u.ro<VecNSp>(1, FID_MassFracs); f.pressure = u.ro<double>(1, FID_pressure);
+   f.SoS = u.ro<double>(2, FID_SoS); f.temperature = u.ro<double>(2, FID_temperature); f.Conserved = u.ro<VecNEq>(2, FID_Conserved);
+   f.Conserved_t = u.rw<VecNEq>(3, FID_Conserved_t);
+   loadMix(args.mix);
+   const htr_rect bc = toRect(u.tile), B = toRect(args.Fluid_bounds);
+   ok(htr_nscbc_outflow(dirIndex(dir), side, &f, &bc, &B, futures[0].get_result<double>(), args.LengthScale, args.PInf, taskStream()));
+}
+// fields of the far-field and incoming-shock tasks (src/prometeo_rhs.cu:1225-1245)
+template<direction dir>
+void farFieldFluid(htr_fluid &f, const Unpacker &u) {
+   const DirFields &D = DIR[dirIndex(dir)];
+   f.*D.nType = u.ro<int>(1, D.fNType); f.*D.m_d = u.ro<double>(1, D.fMd);
+   f.rho = u.ro<double>(0, FID_rho); f.MassFracs = u.ro<VecNSp>(0, FID_MassFracs); f.pressure = u.ro<double>(0, FID_pressure);
+   f.temperature = u.ro<double>(0, FID_temperature); f.velocity = u.ro<Vec3>(0, FID_velocity);
+   f.SoS = u.ro<double>(1, FID_SoS); f.Conserved = u.ro<VecNEq>(1, FID_Conserved);
+   f.Conserved_t = u.rw<VecNEq>(2, FID_Conserved_t);
+}
+template<direction dir, class Args>
+void nscbcFarField(int side, const Args &args, Regions &regions, const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 3 && futures.size() == 1);
+   const Unpacker u(regions, 2, ctx, runtime);
+   htr_fluid f = emptyFluid();
+   htr_bc_fields b = emptyBC();
+   farFieldFluid<dir>(f, u);
+   b.MolarFracs_profile = u.ro<VecNSp>(1, FID_MolarFracs_profile);
+   b.temperature_profile = u.ro<double>(1, FID_temperature_profile);
+   b.velocity_profile = u.ro<Vec3>(1, FID_velocity_profile);
+   loadMix(args.mix);
+   const htr_rect bc = toRect(u.tile);
+   ok(htr_nscbc_farfield(dirIndex(dir), side, &f, &b, &bc, futures[0].get_result<double>(), args.LengthScale, args.PInf, taskStream()));
+}
+} // namespace
+
+#define HTR_NSCBC_BODY(TASK, CALL) \
+   template<direction dir> void TASK<dir>::gpu_base_impl(const Args &args, Regions &regions, \
+                         const std::vector<Future> &futures, Context ctx, Runtime *runtime) { (void)futures; CALL; }
+HTR_NSCBC_BODY(UpdateUsingFluxNSCBCInflowMinusSideTask,    nscbcInflow<dir>(HTR_SIDE_MINUS, args, regions, ctx, runtime))
+HTR_NSCBC_BODY(UpdateUsingFluxNSCBCInflowPlusSideTask,     nscbcInflow<dir>(HTR_SIDE_PLUS, args, regions, ctx, runtime))
+HTR_NSCBC_BODY(UpdateUsingFluxNSCBCOutflowMinusSideTask,   nscbcOutflow<dir>(HTR_SIDE_MINUS, args, regions, futures, ctx, runtime))
+HTR_NSCBC_BODY(UpdateUsingFluxNSCBCOutflowPlusSideTask,    nscbcOutflow<dir>(HTR_SIDE_PLUS, args, regions, futures, ctx, runtime))
+HTR_NSCBC_BODY(UpdateUsingFluxNSCBCFarFieldMinusSideTask,  nscbcFarField<dir>(HTR_SIDE_MINUS, args, regions, futures, ctx, runtime))
+HTR_NSCBC_BODY(UpdateUsingFluxNSCBCFarFieldPlusSideTask,   nscbcFarField<dir>(HTR_SIDE_PLUS, args, regions, futures, ctx, runtime))
+
+template<direction dir>
+void UpdateUsingFluxIncomingShockTask<dir>::gpu_base_impl(const Args &args, Regions &regions,
+                      const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 3 && futures.size() == 1);
+   static_assert(dir == Ydir, "the reference only has the y-plus incoming-shock boundary (src/prometeo_rhs.cc:1064-1074)");
+   const Unpacker u(regions, 2, ctx, runtime);
+   htr_fluid f = emptyFluid();
+   farFieldFluid<dir>(f, u);
+   loadMix(args.mix);
+   double q[1 + nSpec + 10];
+   flattenShock(args.params, q);
+   const htr_rect bc = toRect(u.tile);
+   ok(htr_nscbc_incoming_shock(&f, &bc, futures[0].get_result<double>(), args.LengthScale, q, taskStream()));
+}
+
+// ---- boundary-cell primitive updates (src/prometeo_bc.cu:120-410) ----------------------------------------------------
+template<direction dir>
+void SetNSCBC_InflowBCTask<dir>::gpu_base_impl(const Args &args, Regions &regions,
+                      const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 2);
+   (void)futures;
+   const Unpacker u(regions, 1, ctx, runtime);
+   htr_fluid f = emptyFluid();
+   htr_bc_fields b = emptyBC();
+   f.Conserved = u.ro<VecNEq>(0, FID_Conserved); f.SoS = u.ro<double>(0, FID_SoS);
+   b.MolarFracs_profile = u.ro<VecNSp>(0, FID_MolarFracs_profile);
+   b.temperature_profile = u.ro<double>(0, FID_temperature_profile);
+   b.velocity_profile = u.ro<Vec3>(0, FID_velocity_profile);
+   f.pressure = u.wo<double>(1, FID_pressure); f.temperature = u.wo<double>(1, FID_temperature);
+   f.MolarFracs = u.wo<VecNSp>(1, FID_MolarFracs); f.velocity = u.wo<Vec3>(1, FID_velocity);
+   loadMix(args.mix);
+   const htr_rect bc = toRect(u.tile);
+   ok(htr_set_nscbc_inflow_bc(dirIndex(dir), &f, &b, &bc, args.Pbc, taskStream()));
+}
+
+namespace {
+void outflowPrimitives(htr_fluid &f, const Unpacker &u) {
+   f.Conserved = u.ro<VecNEq>(0, FID_Conserved);
+   f.temperature = u.rw<double>(1, FID_temperature);
+   f.pressure = u.wo<double>(1, FID_pressure); f.MolarFracs = u.wo<VecNSp>(1, FID_MolarFracs); f.velocity = u.wo<Vec3>(1, FID_velocity);
+}
+}
+void SetNSCBC_OutflowBCTask::gpu_base_impl(const Args &args, Regions &regions,
+                      const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 2);
+   (void)futures;
+   const Unpacker u(regions, 1, ctx, runtime);
+   htr_fluid f = emptyFluid();
+   outflowPrimitives(f, u);
+   loadMix(args.mix);
+   const htr_rect bc = toRect(u.tile);
+   ok(htr_set_nscbc_outflow_bc(&f, &bc, taskStream()));
+}
+
+void SetIncomingShockBCTask::gpu_base_impl(const Args &args, Regions &regions,
+                      const std::vector<Future> &futures, Context ctx, Runtime *runtime) {
+   assert(regions.size() == 2);
+   (void)futures;
+   const Unpacker u(regions, 1, ctx, runtime);
+   htr_fluid f = emptyFluid();
+   outflowPrimitives(f, u);
+   loadMix(args.mix);
+   double q[1 + nSpec + 10];
+   flattenShock(args.params, q);
+   const htr_rect bc = toRect(u.tile);
+   ok(htr_set_incoming_shock_bc(&f, &bc, q, taskStream()));
+}
+
 // ---- explicit instantiations, as at the end of the reference's .cu files ------------------------------
 #define HTR_INST3(T) template void T<Xdir>::gpu_base_impl(const Args&, Regions&, const std::vector<Future>&, Context, Runtime*); \
                      template void T<Ydir>::gpu_base_impl(const Args&, Regions&, const std::vector<Future>&, Context, Runtime*); \
@@ -337,3 +485,11 @@ HTR_INST3(UpdateShockSensorTask)
 HTR_INST_TENO(TENO_Op<>)
 HTR_INST_TENO(TENOA_Op<>)
 HTR_INST_TENO(TENOLAD_Op<>)
+HTR_INST3(UpdateUsingFluxNSCBCInflowMinusSideTask)
+HTR_INST3(UpdateUsingFluxNSCBCInflowPlusSideTask)
+HTR_INST3(UpdateUsingFluxNSCBCOutflowMinusSideTask)
+HTR_INST3(UpdateUsingFluxNSCBCOutflowPlusSideTask)
+HTR_INST3(UpdateUsingFluxNSCBCFarFieldMinusSideTask)
+HTR_INST3(UpdateUsingFluxNSCBCFarFieldPlusSideTask)
+template void UpdateUsingFluxIncomingShockTask<Ydir>::gpu_base_impl(const Args&, Regions&, const std::vector<Future>&, Context, Runtime*);
+HTR_INST3(SetNSCBC_InflowBCTask)

@@ -196,6 +196,43 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
                  const double *h_Conserved, const double *h_Conserved_old, double *h_temperature,
                  double *h_Conserved_t, double RK_coeffs0, double RK_coeffs1, double deltaTime, void *stream);
 
+/* ---- non-periodic boundaries: NSCBC right-hand-side tasks and boundary-cell primitive updates ----
+ * Boundary fields of struct Fluid_columns (src/prometeo_types.h:49-113) read by these tasks; same accessor convention as
+ * htr_fluid.  An accessor a task does not read may be {NULL}. */
+typedef struct {
+   htr_acc dudtBoundary, dTdtBoundary;                                  /* Vec3, double */
+   htr_acc velocity_profile, temperature_profile, MolarFracs_profile;   /* Vec3, double, nSpec doubles */
+} htr_bc_fields;
+#define HTR_SIDE_MINUS 0   /* the x/y/zNeg boundary (…MinusSideTask) */
+#define HTR_SIDE_PLUS  1   /* the x/y/zPos boundary (…PlusSideTask) */
+
+/* UpdateUsingFluxNSCBCInflow{Minus,Plus}SideTask<dir> (src/prometeo_rhs.hpp:479-582, addLODIfluxes src/prometeo_rhs.inl:1288-1412,
+ * kernels src/prometeo_rhs.cu:630-845): Conserved_t of the boundary cells `bc` -- zeroed for a supersonic inlet, species
+ * LODI fluxes otherwise. */
+int htr_nscbc_inflow(int dir, int side, const htr_fluid *f, const htr_bc_fields *b, const htr_rect *bc, void *stream);
+/* UpdateUsingFluxNSCBCOutflow{Minus,Plus}SideTask<dir> (src/prometeo_rhs.hpp:584-720, src/prometeo_rhs.inl:1418-1638,
+ * src/prometeo_rhs.cu:863-1170).  MaxMach is the value of the reference's future (CalculateMaxMachNumber). */
+int htr_nscbc_outflow(int dir, int side, const htr_fluid *f, const htr_rect *bc, const htr_rect *bounds,
+                      double MaxMach, double LengthScale, double PInf, void *stream);
+/* UpdateUsingFluxNSCBCFarField{Minus,Plus}SideTask<dir> (src/prometeo_rhs.hpp:722-838, src/prometeo_rhs.inl:1644-1925,
+ * src/prometeo_rhs.cu:1180-1465): far-field state from the *_profile fields. */
+int htr_nscbc_farfield(int dir, int side, const htr_fluid *f, const htr_bc_fields *b, const htr_rect *bc,
+                       double MaxMach, double LengthScale, double PInf, void *stream);
+/* UpdateUsingFluxIncomingShockTask<Ydir> (src/prometeo_rhs.hpp:840-875, src/prometeo_rhs.cc:1076-1138, src/prometeo_rhs.cu:1475-1560):
+ * the y-plus boundary with the upstream state for x < iShock and the downstream state from iShock on.
+ * params (HOST doubles; struct IncomingShockParams, src/prometeo_bc_types.h:46-59, flattened):
+ * iShock, MolarFracs[nSpec], pressure0, temperature0, velocity0[3], pressure1, temperature1, velocity1[3]. */
+int htr_nscbc_incoming_shock(const htr_fluid *f, const htr_rect *bc, double MaxMach, double LengthScale,
+                             const double *params, void *stream);
+/* SetNSCBC_InflowBCTask<dir> (src/prometeo_bc.hpp:113-152, src/prometeo_bc.cc:80-135, src/prometeo_bc.cu:120-218): primitives
+ * of the inflow cells from the profiles; pressure = Pbc where the profile is supersonic, else from the transported density. */
+int htr_set_nscbc_inflow_bc(int dir, const htr_fluid *f, const htr_bc_fields *b, const htr_rect *bc, double Pbc, void *stream);
+/* SetNSCBC_OutflowBCTask (src/prometeo_bc.cc:160-196, src/prometeo_bc.cu:228-290): UpdatePrimitive on the boundary cells. */
+int htr_set_nscbc_outflow_bc(const htr_fluid *f, const htr_rect *bc, void *stream);
+/* SetIncomingShockBCTask (src/prometeo_bc.cc:203-264, src/prometeo_bc.cu:296-410): outflow treatment except for the three
+ * cells iShock-1 .. iShock+1, where the shock is injected; params as for htr_nscbc_incoming_shock. */
+int htr_set_incoming_shock_bc(const htr_fluid *f, const htr_rect *bc, const double *params, void *stream);
+
 /* ---- multi-GPU: block decomposition and ghost-plane exchange (mirrors src/prometeo_partitioner.rg:436-446 tiling,
  * :1107-1352 ghost partitions; Legion/Realm moves the ghosts implicitly in the reference) ----
  * One process per GPU.  The global box is cut into tiles = [tx, ty, tz] equal blocks, rank = cx + tx*(cy + ty*cz), periodic

@@ -14,6 +14,7 @@ using namespace Legion;
 #include "prometeo_chem.hpp"
 #include "prometeo_variables.hpp"
 #include "prometeo_cfl.hpp"
+#include "prometeo_bc.hpp"
 #include "htr_b200.h"
 #include <initializer_list>
 #include <utility>
@@ -201,6 +202,111 @@ RawArgs<      UpdatePrimitiveFromConservedTask::Args> raw; auto &a = raw.get(); 
                                        {FID_lam, &f->lam}, {FID_Di, &f->Di}, {FID_SoS, &f->SoS}}));
 RawArgs<      CalculateMaxSpectralRadiusTask::Args> raw; auto &a = raw.get(); fillMix(a, mix);
       CalculateMaxSpectralRadiusTask::gpu_base_impl(a, R, fut, 0, &rt);
+      return 0; }
+   }
+   return -1;
+}
+
+// Boundary tasks.  task: 0 UpdateUsingFluxNSCBCInflow, 1 ...Outflow, 2 ...FarField (side 0 minus / 1 plus), 3 UpdateUsingFluxIncomingShock
+// (y-plus), 4 SetNSCBC_InflowBC, 5 SetNSCBC_OutflowBC, 6 SetIncomingShockBC.  bc = the plane of boundary cells (the written region);
+// regions and their fields as the reference's bodies open them (src/prometeo_rhs.cc:538-556,692-716,914-934,1085-1100;
+// src/prometeo_bc.cc:89-110,167-180,210-223).  params: the flattened IncomingShockParams of include/htr_b200.h.
+} // extern "C"
+namespace {
+void unflattenShock(IncomingShockParams &P, const double *q) {
+   P.iShock = (int)q[0];
+   for (int s = 0; s < nSpec; s++) P.MolarFracs[s] = q[1 + s];
+   const double *r = q + 1 + nSpec;
+   P.pressure0 = r[0]; P.temperature0 = r[1]; for (int i = 0; i < 3; i++) P.velocity0[i] = r[2 + i];
+   P.pressure1 = r[5]; P.temperature1 = r[6]; for (int i = 0; i < 3; i++) P.velocity1[i] = r[7 + i];
+}
+template<direction dir>
+int runBC(int task, int side, const htr_fluid &f, const htr_bc_fields &b, const htr_rect &bc, const htr_rect &alloc, const htr_rect &B,
+          const void *mix, double MaxMach, double LengthScale, double P, const double *params) {
+   const int d = (dir == Xdir) ? 0 : (dir == Ydir ? 1 : 2);
+   const DirF D = dirFields(f, d), D1 = dirFields(f, d == 0 ? 1 : 0), D2 = dirFields(f, d == 2 ? 1 : 2);
+   std::vector<PhysicalRegion> R;
+   std::vector<Future> fut;
+   Runtime rt;
+   Future ft; ft.v = MaxMach;
+   #define HTR_RUN_SIDE(MINUS, PLUS, FILL) \
+      if (side == 0) { RawArgs<typename MINUS<dir>::Args> raw; auto &a = raw.get(); fillMix(a, mix); FILL; MINUS<dir>::gpu_base_impl(a, R, fut, 0, &rt); } \
+      else           { RawArgs<typename PLUS<dir>::Args> raw; auto &a = raw.get(); fillMix(a, mix); FILL; PLUS<dir>::gpu_base_impl(a, R, fut, 0, &rt); }
+   switch (task) {
+   case 0:
+      R.push_back(region(alloc, false, {{FID_MassFracs, &f.MassFracs}, {FID_pressure, &f.pressure}, {FID_velocity, &f.velocity}}));
+      R.push_back(region(bc, true, {{D.nType, D.aNType}, {D.m_d, D.aMd}, {FID_rho, &f.rho}, {FID_SoS, &f.SoS}, {FID_temperature, &f.temperature},
+                                    {FID_dudtBoundary, &b.dudtBoundary}, {FID_dTdtBoundary, &b.dTdtBoundary}}));
+      R.push_back(region(bc, true, {{FID_Conserved_t, &f.Conserved_t}}));
+      HTR_RUN_SIDE(UpdateUsingFluxNSCBCInflowMinusSideTask, UpdateUsingFluxNSCBCInflowPlusSideTask, (void)0)
+      return 0;
+   case 1:
+      R.push_back(region(alloc, false, {{FID_velocity, &f.velocity}}));
+      R.push_back(region(alloc, false, {{D.nType, D.aNType}, {D1.nType, D1.aNType}, {D2.nType, D2.aNType}, {D.m_d, D.aMd}, {D1.m_d, D1.aMd}, {D2.m_d, D2.aMd},
+                                        {FID_rho, &f.rho}, {FID_mu, &f.mu}, {FID_MassFracs, &f.MassFracs}, {FID_pressure, &f.pressure}}));
+      R.push_back(region(bc, true, {{FID_SoS, &f.SoS}, {FID_temperature, &f.temperature}, {FID_Conserved, &f.Conserved}}));
+      R.push_back(region(bc, true, {{FID_Conserved_t, &f.Conserved_t}}));
+      fut.push_back(ft);
+      HTR_RUN_SIDE(UpdateUsingFluxNSCBCOutflowMinusSideTask, UpdateUsingFluxNSCBCOutflowPlusSideTask,
+                   a.Fluid_bounds = toLegion(B); a.LengthScale = LengthScale; a.PInf = P)
+      return 0;
+   case 2:
+      R.push_back(region(alloc, false, {{FID_rho, &f.rho}, {FID_MassFracs, &f.MassFracs}, {FID_pressure, &f.pressure},
+                                        {FID_temperature, &f.temperature}, {FID_velocity, &f.velocity}}));
+      R.push_back(region(bc, true, {{D.nType, D.aNType}, {D.m_d, D.aMd}, {FID_SoS, &f.SoS}, {FID_Conserved, &f.Conserved},
+                                    {FID_MolarFracs_profile, &b.MolarFracs_profile}, {FID_temperature_profile, &b.temperature_profile},
+                                    {FID_velocity_profile, &b.velocity_profile}}));
+      R.push_back(region(bc, true, {{FID_Conserved_t, &f.Conserved_t}}));
+      fut.push_back(ft);
+      HTR_RUN_SIDE(UpdateUsingFluxNSCBCFarFieldMinusSideTask, UpdateUsingFluxNSCBCFarFieldPlusSideTask, a.LengthScale = LengthScale; a.PInf = P)
+      return 0;
+   case 4: {
+      R.push_back(region(bc, true, {{FID_Conserved, &f.Conserved}, {FID_SoS, &f.SoS}, {FID_MolarFracs_profile, &b.MolarFracs_profile},
+                                    {FID_temperature_profile, &b.temperature_profile}, {FID_velocity_profile, &b.velocity_profile}}));
+      R.push_back(region(bc, true, {{FID_pressure, &f.pressure}, {FID_temperature, &f.temperature}, {FID_MolarFracs, &f.MolarFracs}, {FID_velocity, &f.velocity}}));
+      RawArgs<typename SetNSCBC_InflowBCTask<dir>::Args> raw; auto &a = raw.get(); fillMix(a, mix); a.Pbc = P;
+      SetNSCBC_InflowBCTask<dir>::gpu_base_impl(a, R, fut, 0, &rt);
+      return 0; }
+   }
+   #undef HTR_RUN_SIDE
+   (void)params;
+   return -1;
+}
+} // namespace
+
+extern "C" {
+int htr_adapter_run_bc(int task, int dir, int side, const htr_fluid *f, const htr_bc_fields *b, const htr_rect *bc, const htr_rect *alloc,
+                       const htr_rect *bounds, const void *mix, double MaxMach, double LengthScale, double P, const double *params, void *stream) {
+   Realm::Cuda::stub_task_stream() = stream;
+   if (task <= 2 || task == 4) {
+      if (dir == 0) return runBC<Xdir>(task, side, *f, *b, *bc, *alloc, *bounds, mix, MaxMach, LengthScale, P, params);
+      if (dir == 1) return runBC<Ydir>(task, side, *f, *b, *bc, *alloc, *bounds, mix, MaxMach, LengthScale, P, params);
+      return runBC<Zdir>(task, side, *f, *b, *bc, *alloc, *bounds, mix, MaxMach, LengthScale, P, params);
+   }
+   std::vector<PhysicalRegion> R;
+   std::vector<Future> fut;
+   Runtime rt;
+   switch (task) {
+   case 3: {
+      R.push_back(region(*alloc, false, {{FID_rho, &f->rho}, {FID_MassFracs, &f->MassFracs}, {FID_pressure, &f->pressure},
+                                         {FID_temperature, &f->temperature}, {FID_velocity, &f->velocity}}));
+      R.push_back(region(*bc, true, {{FID_nType_y, &f->nType_y}, {FID_deta_d, &f->deta_d}, {FID_SoS, &f->SoS}, {FID_Conserved, &f->Conserved}}));
+      R.push_back(region(*bc, true, {{FID_Conserved_t, &f->Conserved_t}}));
+      Future ft; ft.v = MaxMach; fut.push_back(ft);
+      RawArgs<UpdateUsingFluxIncomingShockTask<Ydir>::Args> raw; auto &a = raw.get(); fillMix(a, mix);
+      a.LengthScale = LengthScale; unflattenShock(a.params, params);
+      UpdateUsingFluxIncomingShockTask<Ydir>::gpu_base_impl(a, R, fut, 0, &rt);
+      return 0; }
+   case 5: case 6: {
+      R.push_back(region(*bc, true, {{FID_Conserved, &f->Conserved}}));
+      R.push_back(region(*bc, true, {{FID_temperature, &f->temperature}, {FID_pressure, &f->pressure}, {FID_MolarFracs, &f->MolarFracs}, {FID_velocity, &f->velocity}}));
+      if (task == 5) {
+         RawArgs<SetNSCBC_OutflowBCTask::Args> raw; auto &a = raw.get(); fillMix(a, mix);
+         SetNSCBC_OutflowBCTask::gpu_base_impl(a, R, fut, 0, &rt);
+      } else {
+         RawArgs<SetIncomingShockBCTask::Args> raw; auto &a = raw.get(); fillMix(a, mix); unflattenShock(a.params, params);
+         SetIncomingShockBCTask::gpu_base_impl(a, R, fut, 0, &rt);
+      }
       return 0; }
    }
    return -1;

@@ -35,6 +35,12 @@ typedef struct {
    double  *DucrosSensor;
 } htr_oracle_fields;
 
+/* Boundary fields used by the NSCBC tasks (struct Fluid_columns, src/prometeo_types.h:49-113); dense over the same box. */
+typedef struct {
+   double *dudtBoundary, *dTdtBoundary;                                /* Vec3, double */
+   double *velocity_profile, *temperature_profile, *MolarFracs_profile; /* Vec3, double, VecNSp */
+} htr_oracle_bc_fields;
+
 /* Euler schemes (src/config_schema.lua EulerSchemes; task families src/prometeo_rhs.hpp). */
 enum { HTR_SCHEME_HYBRID = 0, HTR_SCHEME_TENO = 1, HTR_SCHEME_TENOA = 2,
        HTR_SCHEME_TENOLAD = 3, HTR_SCHEME_SKEWSYMMETRIC = 4 };
@@ -75,6 +81,21 @@ void htr_oracle_ducros_sensor(const htr_oracle_fields *f, double vorticityScale)
 void htr_oracle_shock_sensor(int dir, const htr_oracle_fields *f);
 void htr_oracle_add_chemistry_sources(const htr_oracle_fields *f);
 void htr_oracle_update_chemistry(const htr_oracle_fields *f, double Integrator_deltaTime);
+/* NSCBC right-hand-side tasks (src/prometeo_rhs.inl:1285-1930) and boundary-cell primitive updates (src/prometeo_bc.cc:80-264)
+ * over the box lo..hi of boundary cells.  side 0 = minus (left) boundary, 1 = plus.  Incoming shock: the y-plus boundary;
+ * params = iShock, MolarFracs[nSpec], pressure0, temperature0, velocity0[3], pressure1, temperature1, velocity1[3]. */
+void htr_oracle_nscbc_inflow(int dir, int side, const htr_oracle_fields *f, const htr_oracle_bc_fields *b,
+                             const int64_t *lo, const int64_t *hi);
+void htr_oracle_nscbc_outflow(int dir, int side, const htr_oracle_fields *f, const int64_t *lo, const int64_t *hi,
+                              double MaxMach, double LengthScale, double PInf);
+void htr_oracle_nscbc_farfield(int dir, int side, const htr_oracle_fields *f, const htr_oracle_bc_fields *b,
+                               const int64_t *lo, const int64_t *hi, double MaxMach, double LengthScale, double PInf);
+void htr_oracle_incoming_shock(const htr_oracle_fields *f, const int64_t *lo, const int64_t *hi,
+                               double MaxMach, double LengthScale, const double *params);
+void htr_oracle_set_nscbc_inflow_bc(int dir, const htr_oracle_fields *f, const htr_oracle_bc_fields *b,
+                                    const int64_t *lo, const int64_t *hi, double Pbc);
+void htr_oracle_set_nscbc_outflow_bc(const htr_oracle_fields *f, const int64_t *lo, const int64_t *hi);
+void htr_oracle_set_incoming_shock_bc(const htr_oracle_fields *f, const int64_t *lo, const int64_t *hi, const double *params);
 void htr_oracle_update_primitive_from_conserved(const htr_oracle_fields *f);
 void htr_oracle_update_properties_from_primitive(const htr_oracle_fields *f);
 void htr_oracle_update_conserved_from_primitive(const htr_oracle_fields *f);

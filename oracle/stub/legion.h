@@ -135,7 +135,18 @@ namespace Legion {
       static void preregister_task_variant(const TaskVariantRegistrar&, const char*) {}
       static LayoutConstraintID preregister_layout(const LayoutConstraintRegistrar&) { return 0; }
    };
-   template<typename T> class SumReduction {};
+   typedef int ReductionOpID;
+   // Legion's built-in sum reduction: the primary template covers the scalar types, src/prometeo_redop.inl specialises
+   // apply / fold for Vec3, VecNSp, ...
+   template<typename T> class SumReduction {
+   public:
+      typedef T LHS;
+      typedef T RHS;
+      template<bool EXCLUSIVE> static void apply(LHS &lhs, RHS rhs);
+      template<bool EXCLUSIVE> static void fold(RHS &rhs1, RHS rhs2);
+   };
+   template<typename T> template<bool EXCLUSIVE> inline void SumReduction<T>::apply(LHS &lhs, RHS rhs) { lhs += rhs; }
+   template<typename T> template<bool EXCLUSIVE> inline void SumReduction<T>::fold(RHS &rhs1, RHS rhs2) { rhs1 += rhs2; }
    // GPU variants return a DeferredValue whose storage is device-visible; the stub keeps a caller-settable pointer
    template<typename T> struct DeferredValue {
       T v; T *p;
@@ -187,7 +198,37 @@ namespace Legion {
       FT& operator[](const Point<1, T> &p) const { return *(FT*)(base + p.x*sx); }
       FT& operator[](coord_t i) const { return *(FT*)(base + i*sx); }
    };
+   // reduction accessor: acc[i] <<= v folds v with the reduction operator (src/prometeo_bc.hpp:85-88 is the only user here)
+   template<typename REDOP, bool EXCLUSIVE>
+   struct StubReducer {
+      typename REDOP::LHS *lhs;
+      void operator<<=(const typename REDOP::RHS &v) const { REDOP::template apply<EXCLUSIVE>(*lhs, v); }
+   };
    template<typename REDOP, bool EXCLUSIVE, int N, typename T = coord_t, typename A = void>
-   struct ReductionAccessor {};
+   struct ReductionAccessor {
+      char *base; coord_t sx;
+      ReductionAccessor() : base(0), sx(0) {}
+      ReductionAccessor(const PhysicalRegion&, FieldID, ReductionOpID) : base(0), sx(0) {}
+      StubReducer<REDOP, EXCLUSIVE> operator[](coord_t i) const { return StubReducer<REDOP, EXCLUSIVE>{(typename REDOP::LHS*)(base + i*sx)}; }
+   };
+   // bit casts used by the compare-and-swap loops of the reduction operators (src/prometeo_redop.inl)
+   namespace TypePunning {
+      template<typename T> class Pointer {
+         void *p;
+      public:
+         Pointer(void *ptr) : p(ptr) {}
+         operator T*() const { return (T*)p; }
+         T operator[](size_t i) const { T v; memcpy(&v, (char*)p + i*sizeof(T), sizeof(T)); return v; }
+      };
+      template<typename T1, typename T2> class Alias {
+         union { T1 a; T2 b; } u;
+      public:
+         Alias() { memset(&u, 0, sizeof(u)); }
+         void load(const Pointer<T1> &ptr) { u.a = ptr[0]; }
+         T1 as_one() const { return u.a; }
+         T2 as_two() const { return u.b; }
+         Alias& operator=(T2 v) { u.b = v; return *this; }
+      };
+   }
 }
 #endif

@@ -34,6 +34,19 @@ class OracleFields(C.Structure):
                [(n, C.c_void_p) for n, _, _ in FIELD_SPECS]
 
 
+# boundary fields of the NSCBC tasks (oracle/htr_oracle_api.h: htr_oracle_bc_fields)
+BC_FIELD_SPECS = [("dudtBoundary", 3), ("dTdtBoundary", 0), ("velocity_profile", 3), ("temperature_profile", 0),
+                  ("MolarFracs_profile", "S")]
+
+
+class OracleBCFields(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n, _ in BC_FIELD_SPECS]
+
+
+def alloc_bc_fields(nx, ny, nz, nspec):
+    return {name: np.zeros((nz, ny, nx) if c == 0 else (nz, ny, nx, ncomp(c, nspec))) for name, c in BC_FIELD_SPECS}
+
+
 def ncomp(c, nspec):
     return {0: 1, 3: 3, "S": nspec, "E": nspec + 4}[c]
 
@@ -184,6 +197,64 @@ class Oracle:
 
     def max_spectral_radius(self, f):
         return self.lib.htr_oracle_max_spectral_radius(C.byref(self._struct(f)))
+
+    # ---- non-periodic boundaries (oracle/ref_bc_driver.cc) ----
+    @staticmethod
+    def _bc_struct(nspec, bcf):
+        s = OracleBCFields()
+        for name, c in BC_FIELD_SPECS:
+            a = bcf[name]
+            assert a.flags["C_CONTIGUOUS"] and a.dtype == np.float64, name
+            setattr(s, name, a.ctypes.data)
+        return s
+
+    @staticmethod
+    def _box(lo, hi):
+        return (C.c_int64 * 3)(*lo), (C.c_int64 * 3)(*hi)
+
+    def nscbc_inflow(self, f, bcf, d, side, lo, hi):
+        L = self.lib.htr_oracle_nscbc_inflow
+        L.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        l, h = self._box(lo, hi)
+        L(d, side, C.byref(self._struct(f)), C.byref(self._bc_struct(self.nspec, bcf)), l, h)
+
+    def nscbc_outflow(self, f, d, side, lo, hi, MaxMach, LengthScale, PInf):
+        L = self.lib.htr_oracle_nscbc_outflow
+        L.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double]
+        l, h = self._box(lo, hi)
+        L(d, side, C.byref(self._struct(f)), l, h, MaxMach, LengthScale, PInf)
+
+    def nscbc_farfield(self, f, bcf, d, side, lo, hi, MaxMach, LengthScale, PInf):
+        L = self.lib.htr_oracle_nscbc_farfield
+        L.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_double]
+        l, h = self._box(lo, hi)
+        L(d, side, C.byref(self._struct(f)), C.byref(self._bc_struct(self.nspec, bcf)), l, h, MaxMach, LengthScale, PInf)
+
+    def incoming_shock(self, f, lo, hi, MaxMach, LengthScale, params):
+        L = self.lib.htr_oracle_incoming_shock
+        L.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_void_p]
+        l, h = self._box(lo, hi)
+        q = np.ascontiguousarray(params, dtype=np.float64)
+        L(C.byref(self._struct(f)), l, h, MaxMach, LengthScale, q.ctypes.data)
+
+    def set_nscbc_inflow_bc(self, f, bcf, d, lo, hi, Pbc):
+        L = self.lib.htr_oracle_set_nscbc_inflow_bc
+        L.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double]
+        l, h = self._box(lo, hi)
+        L(d, C.byref(self._struct(f)), C.byref(self._bc_struct(self.nspec, bcf)), l, h, Pbc)
+
+    def set_nscbc_outflow_bc(self, f, lo, hi):
+        L = self.lib.htr_oracle_set_nscbc_outflow_bc
+        L.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        l, h = self._box(lo, hi)
+        L(C.byref(self._struct(f)), l, h)
+
+    def set_incoming_shock_bc(self, f, lo, hi, params):
+        L = self.lib.htr_oracle_set_incoming_shock_bc
+        L.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        l, h = self._box(lo, hi)
+        q = np.ascontiguousarray(params, dtype=np.float64)
+        L(C.byref(self._struct(f)), l, h, q.ctypes.data)
 
     def rhs(self, f, scheme, diffusion=True, chemistry=False, RK0=1.0, RK1=0.0, dt=0.0):
         """One UpdateDerivatives pass in the reference's task order

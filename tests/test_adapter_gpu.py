@@ -113,3 +113,85 @@ def test_every_adapter_task_matches_the_direct_call(cfg):
     if mix != "ConstPropMix":
         fl.t["Conserved_t"].zero_()
         compare(["Conserved", "Conserved_t_old", "temperature"], lambda: s.UpdateChemistry(fl, 1e-4, tile=tile), lambda: via_adapter(9, 0, 1e-4))
+
+
+@pytest.mark.parametrize("cfg", [CP, AIR], ids=["constprop", "air"])
+def test_boundary_adapter_tasks_match_the_direct_calls(cfg):
+    """The NSCBC right-hand-side tasks and the boundary-cell primitive updates (src/prometeo_rhs.cu:625-1560,
+    src/prometeo_bc.cu:120-410) through T::gpu_base_impl over stub regions -- the written region is the plane of boundary
+    cells, the interior neighbours come with the sparse Fluid / ghost regions -- against the direct C-ABI calls, bit for bit."""
+    from htr_solver_b200 import halo
+    from htr_solver_b200.bc import BCFields, BoundaryTasks, shock_params
+    mix = cfg["type"]
+    A = adapter(mix)
+    A.htr_adapter_run_bc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p,
+                                     C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+    o = oracle_for(cfg)
+    n = (20, 16, 12)
+    f = host_state(o, n, cfg, species_wave=1.0 if mix != "ConstPropMix" else 0.0, front=0.3)
+    c = f["SoS"]
+    f["velocity"][..., 0] = c*np.linspace(-1.6, 1.6, n[1])[None, :, None]
+    f["velocity"][..., 1] = c*np.linspace(-1.6, 1.6, n[2])[:, None, None]
+    f["velocity"][..., 2] = c*np.linspace(-1.6, 1.6, n[0])[None, None, :]
+    o.update_conserved_from_primitive(f)
+    s = htr.Solver(cfg)
+    fl = s.new_fluid(*n, halo=halo.HALO, origin=(7, -3, 40))
+    fl.upload(f)
+    halo.exchange([t for k, t in fl.t.items()], n, 0, (1, 1, 1), None)
+    bcf = BCFields(fl)
+    rng = np.random.default_rng(5)
+    X = f["MolarFracs"]*(1.0 + 0.3*rng.random(f["MolarFracs"].shape))
+    bcf.upload({"dudtBoundary": rng.standard_normal(f["velocity"].shape), "dTdtBoundary": rng.standard_normal(c.shape),
+                "velocity_profile": f["velocity"]*1.1, "temperature_profile": f["temperature"]*1.05,
+                "MolarFracs_profile": X/X.sum(axis=-1, keepdims=True)})
+    bt = BoundaryTasks(s)
+    o3, h = fl.origin, halo.HALO
+    alloc = htr.Rect.make((o3[0] - h, o3[1] - h, o3[2] - h), (o3[0] + n[0] - 1 + h, o3[1] + n[1] - 1 + h, o3[2] + n[2] - 1 + h))
+    nowrap = htr.Rect.make((-2 ** 40,) * 3, (2 ** 40,) * 3)
+    side_stream = torch.cuda.Stream()
+    P0 = float(f["pressure"].mean()); T0 = float(f["temperature"].mean()); c0 = float(c.mean())
+    q = shock_params(o3[0] + n[0]//2, np.full(o.nspec, 1.0/o.nspec), P0, T0, (2*c0, -0.3*c0, 0.0), 2.5*P0, 1.4*T0, (1.5*c0, -0.6*c0, 0.0))
+
+    def plane(d, side):
+        lo = list(o3); hi = [o3[i] + n[i] - 1 for i in range(3)]
+        lo[d] = hi[d] = (o3[d] if side == 0 else o3[d] + n[d] - 1)
+        return htr.Rect.make(lo, hi)
+
+    def via_adapter(task, d, side, bc, MaxMach=0.0, L=0.0, P=0.0):
+        torch.cuda.synchronize()
+        rc = A.htr_adapter_run_bc(task, d, side, C.byref(fl.struct()), C.byref(bcf.struct()), C.byref(bc), C.byref(alloc), C.byref(nowrap),
+                                  s.mix_bytes, MaxMach, L, P, q.ctypes.data, C.c_void_p(side_stream.cuda_stream))
+        assert rc == 0
+        side_stream.synchronize()
+
+    def compare(out_names, direct, adapted):
+        keep = {k: fl.t[k].clone() for k in out_names}
+        got = []
+        for fn in (direct, adapted):
+            for k in out_names:
+                fl.t[k].copy_(keep[k])
+            fn()
+            torch.cuda.synchronize()
+            got.append({k: fl.t[k].clone() for k in out_names})
+        for k in out_names:
+            fl.t[k].copy_(keep[k])
+            assert torch.equal(got[0][k], got[1][k]), k
+        assert any(not torch.equal(got[0][k], keep[k]) for k in out_names)      # the task wrote something
+    fl.t["Conserved_t"].fill_(3.0)
+    prim = ["pressure", "temperature", "MolarFracs", "velocity"]
+    for d in range(3):
+        for side in (0, 1):
+            bc = plane(d, side)
+            compare(["Conserved_t"], lambda: bt.UpdateUsingFluxNSCBCInflow(fl, bcf, d, side, bc), lambda: via_adapter(0, d, side, bc))
+            for MaxMach in (0.5, 1.2):
+                compare(["Conserved_t"], lambda: bt.UpdateUsingFluxNSCBCOutflow(fl, d, side, bc, nowrap, MaxMach, 0.7, P0),
+                        lambda: via_adapter(1, d, side, bc, MaxMach, 0.7, P0))
+                compare(["Conserved_t"], lambda: bt.UpdateUsingFluxNSCBCFarField(fl, bcf, d, side, bc, MaxMach, 0.7, P0),
+                        lambda: via_adapter(2, d, side, bc, MaxMach, 0.7, P0))
+        bc = plane(d, 0)
+        compare(prim, lambda: bt.SetNSCBC_InflowBC(fl, bcf, d, bc, 1.3*P0), lambda: via_adapter(4, d, 0, bc, P=1.3*P0))
+    bc = plane(1, 1)
+    compare(["Conserved_t"], lambda: bt.UpdateUsingFluxIncomingShock(fl, bc, 0.5, 0.7, q), lambda: via_adapter(3, 1, 1, bc, 0.5, 0.7))
+    fl.t["temperature"].mul_(1.02)
+    compare(prim, lambda: bt.SetNSCBC_OutflowBC(fl, bc), lambda: via_adapter(5, 1, 1, bc))
+    compare(prim, lambda: bt.SetIncomingShockBC(fl, bc, q), lambda: via_adapter(6, 1, 1, bc))

@@ -80,3 +80,46 @@ def test_no_device_means_error_not_fallback():
         pytest.skip("GPU present")
     with pytest.raises(htr.HTRError):
         htr.Fluid(4, 4, 4, 1)
+
+
+@needs_air
+def test_nscbc_oracle_leaves_a_uniform_state_at_rest_alone():
+    """The reference has no unit test for its NSCBC tasks, so the BC part of the oracle (oracle/ref_bc_driver.cc) is pinned on
+    what the LODI relations must give: on a uniform gas at rest at the target pressure every wave amplitude vanishes, so the
+    outflow, far-field and inflow tasks add nothing; a pressure excess at a subsonic outflow enters only through the relaxation
+    term K (p - PInf) with K = sigma (1 - MaxMach^2) c / L (src/prometeo_rhs.inl:1464-1470)."""
+    from oracle_lib import alloc_fields, alloc_bc_fields
+    from parity import oracle_for
+    cfg = synthetic.AIRMIX_3DPERIODIC
+    o = oracle_for(cfg)
+    nx, ny, nz = 6, 5, 4
+    f = alloc_fields(nx, ny, nz, o.nspec)
+    prim = synthetic.taylor_green((nx, ny, nz), cfg, U=0.0)
+    for k, v in prim.items():
+        f[k][...] = v
+    f["velocity"][...] = 0.0
+    f["pressure"][...] = 1.0
+    f["temperature"][...] = 1.0
+    f["nType_x"][:, :, 0] = 8; f["nType_x"][:, :, -1] = 12        # L_C / R_C
+    o.update_properties_from_primitive(f)
+    o.update_conserved_from_primitive(f)
+    b = alloc_bc_fields(nx, ny, nz, o.nspec)
+    b["velocity_profile"][...] = 0.0
+    b["temperature_profile"][...] = 1.0
+    b["MolarFracs_profile"][...] = f["MolarFracs"]
+    for side, x in ((0, 0), (1, nx - 1)):
+        lo, hi = [x, 0, 0], [x, ny - 1, nz - 1]
+        f["Conserved_t"][...] = 0.0
+        o.nscbc_outflow(f, 0, side, lo, hi, 0.3, 2.0, 1.0)
+        o.nscbc_farfield(f, b, 0, side, lo, hi, 0.3, 2.0, 1.0)
+        o.nscbc_inflow(f, b, 0, side, lo, hi)
+        assert np.abs(f["Conserved_t"]).max() == 0.0
+        # 1 % pressure excess at the outflow: d1 = K dp / (2 c^2) is the only non-zero LODI term besides dM_n
+        o.nscbc_outflow(f, 0, side, lo, hi, 0.3, 2.0, 1.0/1.01)
+        c = f["SoS"][0, 0, x]; rho = f["rho"][0, 0, x]
+        K = 0.25*(1.0 - 0.3**2)*c/2.0
+        d1 = 0.5*K*(1.0 - 1.0/1.01)/c**2
+        Y = f["MassFracs"][0, 0, x]
+        assert np.allclose(f["Conserved_t"][0, 0, x, :o.nspec], -d1*Y, rtol=1e-12, atol=0)
+        dMn = (1 if side == 0 else -1)*K*(1.0 - 1.0/1.01)/(2*rho*c)
+        assert np.isclose(f["Conserved_t"][0, 0, x, o.nspec], -rho*dMn, rtol=1e-12, atol=0)
