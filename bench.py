@@ -511,7 +511,8 @@ def run_gpu(args, rank, world, local_rank):
                 "kernels_ms": kern, "rhs_bytes_per_cell": B,
                 "rhs_achieved_gbs": B * cells_rank * world * args.steps / (ms * 1e-3) / 1e9 / world,
                 "rhs_frac": B * cells_rank * args.steps / (ms * 1e-3) / 1e9 / peak}
-    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry, march=bool(march & 2))
+    listed = not any(kv.replace(" ", "") == "list=0" for kv in args.opt)
+    launches_per_step = htr.core.rhs_launches(scheme, diffusion, chemistry, march=bool(march & 2), listed=listed)
     if exchanger is not None:
         launches_per_step = exchanger.launches_per_step(diffusion, chemistry, scheme)
 

@@ -58,13 +58,17 @@ def ncomp(c, nspec):
     return {0: 1, 3: 3, "S": nspec, "E": nspec + 4}[c]
 
 
-def rhs_launches(scheme, diffusion, chemistry, fast=True, march=True):
-    """Kernels one htr_rhs call launches (csrc/htr_kernels.cu: htr_rhs)."""
-    if fast and march and scheme in ("Hybrid", "SkewSymmetric"):
-        # Euler-z march + its masked pass; plane march + masked Euler y, x (+ masked diffusion z, y, x)
-        return 2 + 3 + (3 if diffusion else 0)
-    if fast and scheme in ("Hybrid", "SkewSymmetric"):
-        return 5 + (5 if diffusion else 0)       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked       # Euler: z+chem, xy, three masked generic passes; diffusion: z, xy, three masked
+def rhs_launches(scheme, diffusion, chemistry, fast=True, march=True, listed=True):
+    """Kernels one htr_rhs call launches (csrc/htr_kernels.cu: htr_rhs).  `march` = the plane-march form ("march" & 2);
+    `listed` = deferred cells from the compacted list (the default): one compaction per mask + one listed pass per direction,
+    against one block-scan pass per direction."""
+    fastpath = fast and scheme in ("Hybrid", "SkewSymmetric")
+    if fastpath and march:
+        # Euler-z march + its deferred pass; plane march + deferred Euler y, x (+ deferred diffusion z, y, x) on one mask
+        return 2 + 3 + (3 if diffusion else 0) + ((1 + 1) if listed else 0)
+    if fastpath:
+        # Euler: z(+chem), xy, three deferred passes over two masks; diffusion: z, xy, three deferred passes over two masks
+        return 5 + (5 if diffusion else 0) + ((2 + (2 if diffusion else 0)) if listed else 0)
     return 1 + (1 if chemistry else 0) + 3 + (3 if diffusion else 0)
 
 
