@@ -366,6 +366,45 @@ def run_gpu(args, rank, world, local_rank):
     cells_rank = n ** 3
     value = cells_rank * world * args.steps / (ms * 1e-3)
 
+    # ---- multi-GPU: where the step goes (each phase alone on the main stream, max over ranks) ----
+    # In the timed step the exchange (NCCL + ghost recovery) runs on a side stream under the inner box; the shells follow.
+    phases = None
+    if exchanger is not None:
+        def phase_ms(fn, k=5):
+            fn()
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(k):
+                fn()
+            b.record()
+            barrier()
+            t = torch.tensor([a.elapsed_time(b) / k], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        def ghost_recovery():
+            for box in exchanger.ghost_boxes:
+                solver.UpdateGhostPrimitiveFromConserved(fl, tile=box)
+                solver.UpdatePropertiesFromPrimitive(fl, tile=box)
+
+        def boxes(bs):
+            for box in bs:
+                solver.UpdateDerivatives(fl, scheme, diffusion, chemistry, (1.0, 0.0), 1e-3, tile=box, bounds=exchanger.nowrap)
+        try:
+            cells = lambda r: int(np.prod([r.hi[i] - r.lo[i] + 1 for i in range(3)]))
+            phases = {"nccl_exchange_ms": phase_ms(lambda: exchanger.nccl.exchange(fl, ["Conserved", "temperature"])),
+                      "ghost_recovery_ms": phase_ms(ghost_recovery),
+                      "inner_box_ms": phase_ms(lambda: boxes([exchanger.inner])),
+                      "shell_boxes_ms": phase_ms(lambda: boxes(exchanger.shells)),
+                      "whole_tile_one_call_ms": phase_ms(lambda: boxes([tile])),
+                      "inner_cells": cells(exchanger.inner), "shell_cells": [cells(b) for b in exchanger.shells],
+                      "ghost_cells": [cells(b) for b in exchanger.ghost_boxes],
+                      "how": "each phase alone on the main stream, CUDA events, mean of 5, max over ranks; in the timed step the "
+                             "exchange and the ghost recovery run on a side stream under the inner box"}
+        except Exception as ex:
+            phases = {"error": repr(ex)[:200]}
+
     # ---- per-kernel durations (CUDA events on the launching stream) for the dominant-kernel roofline ----
     # htr_rhs_parts runs one staged kernel (+ its masked generic pass, a few microseconds when nothing is deferred)
     kern = {}
@@ -548,7 +587,7 @@ def run_gpu(args, rank, world, local_rank):
                        "smooth_fraction": smooth, "l2": "inputs larger than L2 (no flush needed)" if n >= 128 else "inputs may fit L2",
                        "halo": "none (periodic wrap by index)" if world == 1 else "3 ghost planes, NCCL send/recv per step"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-            "roofline": roof, "cpu_baseline": cpu, "parity": parity, "time_step": tstep, "build": solver.L.htr_build_info().decode()}
+            "roofline": roof, "cpu_baseline": cpu, "parity": parity, "time_step": tstep, "phases": phases, "build": solver.L.htr_build_info().decode()}
     emit(json.dumps(line))
 
 
