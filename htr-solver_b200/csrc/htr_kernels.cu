@@ -21,6 +21,7 @@
 #include "htr_fast_bulk.cuh"
 #include "htr_diff_bulk.cuh"
 #include "htr_march.cuh"
+#include "htr_diff_async.cuh"
 
 namespace htr {
 
@@ -282,6 +283,10 @@ static cudaError_t launchMaskedScan(const htr_fluid &f, const htr_rect &tile, co
 // ~80 dependent, component-strided loads per cell on the critical path of every warp), which costs more than the pass it saves.
 static bool g_diff3 = false;
 static bool g_bulk_diffusion = false;   // htr_set_option("bulk_diffusion", 1): TMA bulk staging for the diffusion kernels too
+// htr_set_option("dasync", 1) (default): the diffusion tiles reach shared memory by cp.async row copies (htr_diff_async.cuh:
+// diffusion_async_kernel) instead of the cooperative load/store staging of fast::diffusion_staged_kernel; same bits.
+// Measured on B200, 512^3 AirMix (profiles/r2_v15_*): diffusion z 13.53 -> 12.38 ms, y+x 23.39 -> 21.29 ms.
+static bool g_dasync = true;
 static bool g_no_pipe = false;          // htr_set_option("pipeline", 0): htr_host_rhs without the z-slab copy/compute overlap
 static bool g_no_bulk = false;          // htr_set_option("bulk", 0): cooperative loads instead of TMA bulk copies
 
@@ -425,6 +430,8 @@ static cudaError_t launchFastEuler(bool chem, const htr_fluid &f, const htr_rect
    return cudaSuccess;
 }
 
+static bool makeUniform(const rfluid &rf, const rbox &rt, const rbox &rb, bool hybrid, bool chem, bool diffusion, march::UF &u);
+
 // Conserved_t += diffusion z; += y; += x through the staged kernels + masked generic passes (same scratch,
 // after launchFastEuler has consumed it in stream order; flags [2], [3] were cleared there).
 static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile, const htr_rect &B,
@@ -459,14 +466,25 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
          cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
          cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
       }
+      // cp.async staging on the uniform view of the fields (htr_diff_async.cuh); any other layout takes the cooperative kernels
+      march::UF u;
+      const bool dasync = g_dasync && makeUniform(rf, rt, rb, false, false, true, u);
+      if (dasync && firstUseOnDevice(7)) {
+         cudaFuncSetAttribute(fast::diffusion_async_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ATile<2, TJ>::SMEM);
+         cudaFuncSetAttribute(fast::diffusion_async_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ATile<1, TJ>::SMEM);
+      }
       dim3 gz((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
       if (parts & PART_DZ) {
+         if (dasync) fast::diffusion_async_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::ATile<2, TJ>::SMEM, st>>>(u, maskZ, flags + 2);
+         else
          fast::diffusion_staged_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(rf, rt, rb, maskZ, flags + 2);
          if ((e = cudaGetLastError()) != cudaSuccess) return e;
          if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
       }
       if (!(parts & PART_DXY)) return cudaSuccess;
       dim3 gxy((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
+      if (dasync) fast::diffusion_async_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::ATile<1, TJ>::SMEM, st>>>(u, maskXY, flags + 3);
+      else
       fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
@@ -1075,6 +1093,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "tensor") == 0) { g_no_tensor = (value == 0); return HTR_OK; }
    if (strcmp(name, "list") == 0) { g_no_list = (value == 0); return HTR_OK; }
    if (strcmp(name, "diff3") == 0) { g_diff3 = (value != 0); return HTR_OK; }
+   if (strcmp(name, "dasync") == 0) { g_dasync = (value != 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
    if (strcmp(name, "march") == 0) { if (value < 0 || value > 7) return HTR_EINVAL; g_march = value; return HTR_OK; }

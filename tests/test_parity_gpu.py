@@ -12,6 +12,7 @@ pytestmark = pytest.mark.gpu
 CP = synthetic.CONSTPROP_VISCOUS
 AIR = synthetic.AIRMIX_3DPERIODIC
 EULER_SCHEMES = ["SkewSymmetric", "TENO", "TENOA", "TENOLAD", "Hybrid"]
+DASYNC_DEFAULT = 1      # library default of htr_set_option("dasync") (csrc/htr_kernels.cu: g_dasync)
 
 
 def _sensors(o, f, vs=1.0):
@@ -351,12 +352,15 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         # 4: Euler-z march + plane march without its diffusion phase + staged diffusion ("march" = 5)
         # 5: the default with the fused three-direction diffusion kernel ("diff3" = 1) instead of the two staged ones
         # 6: the default with the deferred cells found by the block scan ("list" = 0) instead of the compacted list
-        for path, (fast, march, diff3, lst) in {1: (1, 3, 0, 1), 2: (1, 0, 0, 1), 3: (1, 1, 0, 1), 4: (1, 5, 0, 1), 5: (1, 1, 1, 1),
-                                                6: (1, 1, 0, 0), 0: (0, 0, 0, 1)}.items():
+        # 7: the default with the other staging of the diffusion tiles ("dasync" flipped: cp.async row copies, csrc/htr_diff_async.cuh,
+        #    vs cooperative loads, csrc/htr_fast.cuh)
+        for path, (fast, march, diff3, lst, flip) in {1: (1, 3, 0, 1, 0), 2: (1, 0, 0, 1, 0), 3: (1, 1, 0, 1, 0), 4: (1, 5, 0, 1, 0),
+                                                      5: (1, 1, 1, 1, 0), 6: (1, 1, 0, 0, 0), 7: (1, 1, 0, 1, 1), 0: (0, 0, 0, 1, 0)}.items():
             s.set_option("fast", fast)
             s.set_option("march", march)
             s.set_option("diff3", diff3)
             s.set_option("list", lst)
+            s.set_option("dasync", DASYNC_DEFAULT ^ flip)
             fl.t["Conserved_t"].fill_(-3.0)
             s.UpdateDerivatives(fl, scheme, diffusion=True, chemistry=chem, RK_coeffs=(0.75, 0.25), deltaTime=1e-3)
             out[path] = fl.download(["Conserved_t"])["Conserved_t"]
@@ -365,6 +369,7 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         s.set_option("march", 1)
         s.set_option("diff3", 0)
         s.set_option("list", 1)
+        s.set_option("dasync", DASYNC_DEFAULT)
     o.rhs(f, scheme, diffusion=True, chemistry=chem, RK0=0.75, RK1=0.25, dt=1e-3)
     scale = np.maximum.reduce([euler_scale(f, d) for d in range(3)])
     if chem:
@@ -374,10 +379,10 @@ def test_staged_rhs_equals_per_task_sequence(cfg, chem, kw, scheme, variant, n):
         scale = scale + np.abs(f["Conserved_t"]).reshape(-1, scale.size).max(axis=0)
         f["Conserved_t"][...] = ref
     if variant == "strict":
-        for k in (1, 2, 3, 4, 5, 6):
+        for k in (1, 2, 3, 4, 5, 6, 7):
             assert np.array_equal(out[k], out[0]), k
     else:
-        for k in (1, 2, 3, 4, 5, 6):
+        for k in (1, 2, 3, 4, 5, 6, 7):
             assert scaled_err(out[k], out[0], scale) <= TOL_FLUX, k
     assert scaled_err(out[1], f["Conserved_t"], scale) <= (TOL_CHEM if chem else TOL_FLUX)
 

@@ -21,6 +21,15 @@ def main():
     rows = list(csv.reader(open(sys.argv[1])))
     hdr, units = rows[0], rows[1]
     idx = [(w, hdr.index(w)) for w in WANT if w in hdr]
+    if '--grep' in sys.argv:      # every metric whose name contains one of the comma-separated patterns, one kernel per block
+        pats = sys.argv[sys.argv.index('--grep') + 1].split(',')
+        ki = hdr.index('Kernel Name')
+        for r in rows[2:]:
+            print('-----', r[ki][:90])
+            for i, h in enumerate(hdr):
+                if any(p in h for p in pats):
+                    print(f"{h:95s} {r[i][:40]} {units[i]}")
+        return
     if '--csv' in sys.argv:
         w = csv.writer(sys.stdout)
         w.writerow([a for a, _ in idx]); w.writerow([units[i] for _, i in idx])
