@@ -82,9 +82,6 @@
 #ifndef HTR_D_TJ
 #define HTR_D_TJ 8
 #endif
-#ifndef HTR_DB_MINB
-#define HTR_DB_MINB 2
-#endif
 #ifndef HTR_D_HOIST
 #define HTR_D_HOIST 0
 #endif

@@ -19,7 +19,6 @@
 #include "htr_pointwise.cuh"
 #include "htr_fast.cuh"
 #include "htr_fast_bulk.cuh"
-#include "htr_diff_bulk.cuh"
 #include "htr_march.cuh"
 #include "htr_diff_async.cuh"
 
@@ -126,8 +125,15 @@ HTR_DEV void fluxBlock(const unsigned bx, const unsigned by, const unsigned bz, 
    }
 }
 
+// resident CTAs per SM the register allocation of the generic per-face kernels aims at (1 = up to 255 registers)
+#ifndef HTR_FLUX_MINB
+#define HTR_FLUX_MINB 1
+#endif
+#ifndef HTR_LIST_MINB
+#define HTR_LIST_MINB 1
+#endif
 template<int dir, int KIND, int SCHEME>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, HTR_FLUX_MINB)
 flux_divergence_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep) {
    fluxBlock<dir, KIND, SCHEME, false>(blockIdx.x, blockIdx.y, blockIdx.z, f, tile, B, ep, nullptr);
 }
@@ -203,7 +209,7 @@ __global__ void __launch_bounds__(256) compact_mask_kernel(const uint8_t *__rest
 }
 
 template<int dir, int KIND, int SCHEME>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, HTR_LIST_MINB)
 listed_flux_kernel(const htr_fluid f, const htr_rect tile, const htr_rect B, const EulerParams ep,
                    const int *__restrict__ list, const int *__restrict__ count) {
    const int n = *count;
@@ -282,11 +288,11 @@ static cudaError_t launchMaskedScan(const htr_fluid &f, const htr_rect &tile, co
 // 13.7 + 23.1 ms -- the operands of the planes p-1 / p+1 are read from global memory inside the flux phase (L2 hits, but
 // ~80 dependent, component-strided loads per cell on the critical path of every warp), which costs more than the pass it saves.
 static bool g_diff3 = false;
-static bool g_bulk_diffusion = false;   // htr_set_option("bulk_diffusion", 1): TMA bulk staging for the diffusion kernels too
 // htr_set_option("dasync", 1) (default): the diffusion tiles reach shared memory by cp.async row copies (htr_diff_async.cuh:
 // diffusion_async_kernel) instead of the cooperative load/store staging of fast::diffusion_staged_kernel; same bits.
 // Measured on B200, 512^3 AirMix (profiles/r2_v15_*): diffusion z 13.53 -> 12.38 ms, y+x 23.39 -> 21.29 ms.
 static bool g_dasync = true;
+static int g_slab_tiles = 0;            // htr_set_option("slab", k): z-slab thickness of htr_host_rhs in z tiles of 7 planes (0 = 14 planes)
 static bool g_no_pipe = false;          // htr_set_option("pipeline", 0): htr_host_rhs without the z-slab copy/compute overlap
 static bool g_no_bulk = false;          // htr_set_option("bulk", 0): cooperative loads instead of TMA bulk copies
 
@@ -442,12 +448,8 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
    int *flags = reinterpret_cast<int*>(scratch);
    uint8_t *maskZ = scratch + 16, *maskXY = maskZ + n[0]*n[1]*n[2];
    const EulerParams ep = {0, 0, 0};
-   if (firstUseOnDevice(2)) {
-      cudaFuncSetAttribute(fast::diffusion_bulk_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<2, TJ>::SMEM);
-      cudaFuncSetAttribute(fast::diffusion_bulk_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DB<1, TJ>::SMEM);
-   }
    cudaError_t e;
-   if (g_diff3 && !g_bulk_diffusion) {
+   if (g_diff3) {
       // all three directions in one pass over Conserved_t (htr_march.cuh: diffusion3_staged_kernel); PART_DXY stands for it
       if (!(parts & PART_DXY)) return cudaSuccess;
       if (firstUseOnDevice(6))
@@ -459,53 +461,33 @@ static cudaError_t launchFastDiffusion(const htr_fluid &f, const htr_rect &tile,
       if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false)) != cudaSuccess) return e;
       return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false);
    }
-   if (!g_bulk_diffusion) {
-      // default: cooperative staging (htr_fast.cuh).  Measured on B200 (profiles/r1_v8_*): the bulk-copy variant below
-      // needs ~90 row copies of 0.3-2.6 KB per CTA and is TMA-issue bound (Dz 3.2 vs 1.9 ms, Dxy 4.2 vs 3.3 ms at 256^3).
-      if (firstUseOnDevice(3)) {
-         cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
-         cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
-      }
-      // cp.async staging on the uniform view of the fields (htr_diff_async.cuh); any other layout takes the cooperative kernels
-      march::UF u;
-      const bool dasync = g_dasync && makeUniform(rf, rt, rb, false, false, true, u);
-      if (dasync && firstUseOnDevice(7)) {
-         cudaFuncSetAttribute(fast::diffusion_async_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ATile<2, TJ>::SMEM);
-         cudaFuncSetAttribute(fast::diffusion_async_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ATile<1, TJ>::SMEM);
-      }
-      dim3 gz((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
-      if (parts & PART_DZ) {
-         if (dasync) fast::diffusion_async_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::ATile<2, TJ>::SMEM, st>>>(u, maskZ, flags + 2);
-         else
-         fast::diffusion_staged_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(rf, rt, rb, maskZ, flags + 2);
-         if ((e = cudaGetLastError()) != cudaSuccess) return e;
-         if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
-      }
-      if (!(parts & PART_DXY)) return cudaSuccess;
-      dim3 gxy((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
-      if (dasync) fast::diffusion_async_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::ATile<1, TJ>::SMEM, st>>>(u, maskXY, flags + 3);
-      else
-      fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
-      if ((e = cudaGetLastError()) != cudaSuccess) return e;
-      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
-      return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false);
+   // (a variant with 1-D TMA row copies existed in round 1: ~90 copies of 0.3-2.6 KB per CTA made it TMA-issue bound,
+   //  Dz 3.2 vs 1.9 ms and Dxy 4.2 vs 3.3 ms at 256^3, profiles/r1_v8_*; removed in round 2)
+   if (firstUseOnDevice(3)) {
+      cudaFuncSetAttribute(fast::diffusion_staged_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<2, TJ>::SMEM);
+      cudaFuncSetAttribute(fast::diffusion_staged_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::DTile<1, TJ>::SMEM);
    }
-   const int bulkOK = bulkEligible({{&rf.rho, 1}, {&rf.mu, 1}, {&rf.lam, 1}, {&rf.temperature, 1}, {&rf.MolarFracs, nSpec},
-                                    {&rf.Di, nSpec}, {&rf.Conserved, nEq}, {&rf.velocity, 3}});
+   // cp.async staging on the uniform view of the fields (htr_diff_async.cuh); any other layout takes the cooperative kernels
+   march::UF u;
+   const bool dasync = g_dasync && makeUniform(rf, rt, rb, false, false, true, u);
+   if (dasync && firstUseOnDevice(7)) {
+      cudaFuncSetAttribute(fast::diffusion_async_kernel<2, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ATile<2, TJ>::SMEM);
+      cudaFuncSetAttribute(fast::diffusion_async_kernel<1, TJ>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fast::ATile<1, TJ>::SMEM);
+   }
+   dim3 gz((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
    if (parts & PART_DZ) {
-      dim3 grid((unsigned)((n[0] + 31)/32), (unsigned)((n[2] + TJ - 2)/(TJ - 1)), (unsigned)n[1]);
-      fast::diffusion_bulk_kernel<2, TJ><<<grid, dim3(32, TJ, 1), fast::DB<2, TJ>::SMEM, st>>>(rf, rt, rb, maskZ, flags + 2, bulkOK);
+      if (dasync) fast::diffusion_async_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::ATile<2, TJ>::SMEM, st>>>(u, maskZ, flags + 2);
+      else        fast::diffusion_staged_kernel<2, TJ><<<gz, dim3(32, TJ, 1), fast::DTile<2, TJ>::SMEM, st>>>(rf, rt, rb, maskZ, flags + 2);
       if ((e = cudaGetLastError()) != cudaSuccess) return e;
       if ((e = launchMasked<2, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskZ, flags + 2, st)) != cudaSuccess) return e;
    }
-   if (parts & PART_DXY) {
-      dim3 grid((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
-      fast::diffusion_bulk_kernel<1, TJ><<<grid, dim3(32, TJ, 1), fast::DB<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3, bulkOK);
-      if ((e = cudaGetLastError()) != cudaSuccess) return e;
-      if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
-      if ((e = launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false)) != cudaSuccess) return e;
-   }
-   return cudaSuccess;
+   if (!(parts & PART_DXY)) return cudaSuccess;
+   dim3 gxy((unsigned)((n[0] + 30)/31), (unsigned)((n[1] + TJ - 2)/(TJ - 1)), (unsigned)n[2]);
+   if (dasync) fast::diffusion_async_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::ATile<1, TJ>::SMEM, st>>>(u, maskXY, flags + 3);
+   else        fast::diffusion_staged_kernel<1, TJ><<<gxy, dim3(32, TJ, 1), fast::DTile<1, TJ>::SMEM, st>>>(rf, rt, rb, maskXY, flags + 3);
+   if ((e = cudaGetLastError()) != cudaSuccess) return e;
+   if ((e = launchMasked<1, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st)) != cudaSuccess) return e;
+   return launchMasked<0, FLUX_DIFFUSION, 0>(f, tile, B, ep, maskXY, flags + 3, st, false);
 }
 
 // ---- z-marching two-pass form (htr_march.cuh) ---------------------------------------------------
@@ -1095,7 +1077,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "diff3") == 0) { g_diff3 = (value != 0); return HTR_OK; }
    if (strcmp(name, "dasync") == 0) { g_dasync = (value != 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
-   if (strcmp(name, "bulk_diffusion") == 0) { g_bulk_diffusion = (value != 0); return HTR_OK; }
+   if (strcmp(name, "slab") == 0) { if (value < 0 || value > 64) return HTR_EINVAL; g_slab_tiles = value; return HTR_OK; }
    if (strcmp(name, "march") == 0) { if (value < 0 || value > 7) return HTR_EINVAL; g_march = value; return HTR_OK; }
    if (strcmp(name, "march_kz") == 0) { if (value < 1) return HTR_EINVAL; g_march_kz = value; return HTR_OK; }
    if (strcmp(name, "march_kp") == 0) { if (value < 1) return HTR_EINVAL; g_march_kp = value; return HTR_OK; }
@@ -1601,7 +1583,7 @@ static void *cellPtr(const htr_acc &a, const htr_rect &t) {
 // The first planes of each stage (whose stencils reach back across the periodic wrap to planes that are uploaded last)
 // and the last ones are done after the last upload: 2 x 8 planes.  A download therefore trails its upload by one slab
 // and 8 planes, and the call takes about max(H2D, D2H) of the whole state plus that lag.
-constexpr int PIPE_MAXSLABS = 64;
+constexpr int PIPE_MAXSLABS = 128;
 struct HostPipe { cudaStream_t up, down; cudaEvent_t evUp[PIPE_MAXSLABS], evR[PIPE_MAXSLABS + 2], evStart, evDone; bool ok; };
 static HostPipe g_pipe_dev[HTR_MAX_DEVICES] = {};
 #define g_pipe g_pipe_dev[curDev()]
@@ -1633,7 +1615,10 @@ int htr_host_rhs(int scheme, int diffusion, int chemistry, int update_sensors, d
    const bool sensors = update_sensors && scheme == HTR_SCHEME_HYBRID;
    // slab thickness: a multiple of the planes one CTA of the z kernels updates (Euler-z and diffusion-z: 7)
    constexpr int64_t TZ = fast::ZT_Z - 1;
-   int64_t T = (nz >= 400) ? 4*TZ : 2*TZ;
+   // 14 planes: the download of a slab trails its upload by one slab + 8 planes, and that lag is what the call costs beyond
+   // max(H2D, D2H); measured on B200 at 512^3 (profiles/r2_v18_*): 28-plane slabs 236.3 ms, 14 planes 230.7, 7 planes 230.7
+   int64_t T = 2*TZ;
+   if (g_slab_tiles > 0) T = g_slab_tiles*TZ;        // htr_set_option("slab", k): slabs of 7k planes
    while ((nz + T - 1)/T > PIPE_MAXSLABS) T += TZ;
    const bool pipelined = nz >= 60 && !g_no_pipe && pipeInit();
    const int ns = pipelined ? (int)((nz + T - 1)/T) : 1;
