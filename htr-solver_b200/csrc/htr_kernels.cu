@@ -57,6 +57,15 @@ HTR_DEV void eulerFace(double *Flux, const htr_fluid &f, const Pt &p, int t, con
    else if (SCHEME == HTR_SCHEME_TENOLAD) tenoFaceFlux<dir, OP_TENOLAD>(Flux, f, p, t, B, ep.RK0, ep.RK1, lim_f);
 }
 
+} // namespace htr
+#include "htr_teno_coop.cuh"     // eight lanes per TENO face (uses EulerParams, kgFaceFlux and the accessors above)
+namespace htr {
+// htr_set_option("coop", 1): the lane-cooperative TENO kernels (eight lanes per face) instead of the one-thread-per-face ones.
+// Off by default: bit-identical (tests/test_coop_gpu.py) but SLOWER on B200 (profiles/r2_v21_*): 128^3 ConstPropMix TENO 8.35 vs
+// 4.14 ms per RHS, air256_front 29.6 vs 10.6 ms, air512_front 152.0 vs 71.6 ms -- see htr_teno_coop.cuh for why.
+static bool g_coop = false;
+static int numSMs();
+
 // KIND = FLUX_EULER (SCHEME selects the reconstruction) or FLUX_DIFFUSION
 // MASKED: only the cells flagged in `mask` (dense over the tile, see htr_fast.cuh) are updated and only
 // the faces they need are evaluated; a block without flagged cells returns at once.
@@ -161,6 +170,17 @@ static cudaError_t launchFlux(const htr_fluid &f, const htr_rect &tile, const ht
    const int C[3] = {FB::X - (dir == 0), FB::Y - (dir == 1), FB::Z - (dir == 2)};
    dim3 grid((unsigned)((n[0] + C[0] - 1)/C[0]), (unsigned)((n[1] + C[1] - 1)/C[1]), (unsigned)((n[2] + C[2] - 1)/C[2]));
    dim3 block(FB::X, FB::Y, FB::Z);
+   if constexpr (KIND == FLUX_EULER && (SCHEME == HTR_SCHEME_TENO || SCHEME == HTR_SCHEME_TENOA || SCHEME == HTR_SCHEME_TENOLAD)) {
+      if (g_coop) {       // runs of 8 cells along dir, one group of eight lanes each (htr_teno_coop.cuh)
+         constexpr int RUN = 8;
+         const int64_t runs = ((n[dir] + RUN - 1)/RUN)*(n[0]*n[1]*n[2]/n[dir]);
+         int perSM = 1;
+         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, coop::euler_coop_kernel<dir, SCHEME, false>, coop::GL*coop::GROUPS, 0) != cudaSuccess || perSM < 1) perSM = 1;
+         const int64_t want = (runs + coop::GROUPS - 1)/coop::GROUPS, cap = (int64_t)numSMs()*perSM*8;
+         coop::euler_coop_kernel<dir, SCHEME, false><<<(unsigned)(want < cap ? want : cap), coop::GL*coop::GROUPS, 0, st>>>(f, tile, B, ep, nullptr, nullptr, RUN);
+         return cudaGetLastError();
+      }
+   }
    flux_divergence_kernel<dir, KIND, SCHEME><<<grid, block, 0, st>>>(f, tile, B, ep);
    return cudaGetLastError();
 }
@@ -257,6 +277,13 @@ static cudaError_t launchMasked(const htr_fluid &f, const htr_rect &tile, const 
          compact_mask_kernel<<<(unsigned)(g < (int64_t)numSMs()*8 ? g : (int64_t)numSMs()*8), 256, 0, st>>>(mask, cells, flag, list, count);
       }
       int perSM = 1;
+      if constexpr (KIND == FLUX_EULER && SCHEME != HTR_SCHEME_SKEWSYMMETRIC) {
+         if (g_coop) {    // a deferred Euler cell = a run of one cell for a group of eight lanes (htr_teno_coop.cuh)
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, coop::euler_coop_kernel<dir, SCHEME, true>, coop::GL*coop::GROUPS, 0) != cudaSuccess || perSM < 1) perSM = 1;
+            coop::euler_coop_kernel<dir, SCHEME, true><<<(unsigned)(numSMs()*perSM), coop::GL*coop::GROUPS, 0, st>>>(f, tile, B, ep, list, count, 1);
+            return cudaGetLastError();
+         }
+      }
       if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, listed_flux_kernel<dir, KIND, SCHEME>, 128, 0) != cudaSuccess || perSM < 1) perSM = 1;
       listed_flux_kernel<dir, KIND, SCHEME><<<(unsigned)(numSMs()*perSM), 128, 0, st>>>(f, tile, B, ep, list, count);
       return cudaGetLastError();
@@ -1076,6 +1103,7 @@ int htr_set_option(const char *name, int value) {
    if (strcmp(name, "list") == 0) { g_no_list = (value == 0); return HTR_OK; }
    if (strcmp(name, "diff3") == 0) { g_diff3 = (value != 0); return HTR_OK; }
    if (strcmp(name, "dasync") == 0) { g_dasync = (value != 0); return HTR_OK; }
+   if (strcmp(name, "coop") == 0) { g_coop = (value != 0); return HTR_OK; }
    if (strcmp(name, "pipeline") == 0) { g_no_pipe = (value == 0); return HTR_OK; }
    if (strcmp(name, "slab") == 0) { if (value < 0 || value > 64) return HTR_EINVAL; g_slab_tiles = value; return HTR_OK; }
    if (strcmp(name, "march") == 0) { if (value < 0 || value > 7) return HTR_EINVAL; g_march = value; return HTR_OK; }

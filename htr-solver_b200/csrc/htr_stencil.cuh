@@ -210,6 +210,80 @@ HTR_DEV double tenoReconstruct(double ym2, double ym1, double y, double yp1, dou
    return assemble<plus>(ym2, ym1, y, yp1, yp2, yp3, t, b1, b2, b3, b4);
 }
 
+// The same reconstruction with the upwind side as a RUN-TIME flag, for the lane-cooperative TENO kernels
+// (htr_teno_coop.cuh), where the lanes of a warp reconstruct plus and minus fields side by side and must not diverge.
+// Bit-identical with tenoReconstruct<OP, plus>: smoothness<false>(a..f) is smoothness<true>(f..a) expression for expression
+// (same operand order in every sum), the Ren indicator and `assemble` use the inputs in the given order with the tables
+// of the chosen side.
+template<int OP>
+HTR_DEV double tenoReconstructRT(const bool plus, double ym2, double ym1, double y, double yp1, double yp2, double yp3, int t) {
+   constexpr double eps = (OP == OP_TENO) ? tenPow(-10) : (OP == OP_TENOA) ? tenPow(-8) : tenPow(-16);
+   const Smoothness S = smoothness<true>(plus ? ym2 : yp3, plus ? ym1 : yp2, plus ? y : yp1, plus ? yp1 : y, plus ? yp2 : ym1, plus ? yp3 : ym2);
+   double Co[4];
+   HTR_UNROLL
+   for (int k = 0; k < 4; k++) Co[k] = plus ? c_Coeffs_Plus[t][k] : c_Coeffs_Minus[t][k];
+   const double chi1 = S.tau6/(S.s1 + eps);
+   const double chi2 = S.tau6/(S.s2 + eps);
+   const double chi3 = S.tau6/(S.s3 + eps);
+   const double chi4 = S.tau6/(S.s4 + eps);
+   double a1 = pow6(1 + chi1), a2 = pow6(1 + chi2), a3 = pow6(1 + chi3), a4 = pow6(1 + chi4);
+   auto drop = [&]() {
+      if (Co[0] < 1e-10) a1 = 0.0;
+      if (Co[1] < 1e-10) a2 = 0.0;
+      if (Co[2] < 1e-10) a3 = 0.0;
+      if (Co[3] < 1e-10) a4 = 0.0;
+   };
+   double cut_off;
+   if (OP == OP_TENO) {
+      drop();
+      cut_off = 1e-6;
+   } else if (OP == OP_TENOA) {
+      if (t == Std_node) {
+         constexpr double Ren_r_c = 0.2;
+         constexpr double Ren_eps = 0.9*Ren_r_c*1e-16/(1.0 - 0.9*Ren_r_c);
+         constexpr double Ren_irc = 1.0/Ren_r_c;
+         constexpr double Smooth_pow = 9.5, Shock_pow = 6.0, Diff_pow = Smooth_pow - Shock_pow;
+         const double v2 = fabs(ym1 - ym2), v3 = fabs(y - ym1), v4 = fabs(yp1 - y), v5 = fabs(yp2 - yp1), v6 = fabs(yp3 - yp2);
+         double eta = fmin((2*v2*v3 + Ren_eps)/(v2*v2 + v3*v3 + Ren_eps),
+                           (2*v3*v4 + Ren_eps)/(v3*v3 + v4*v4 + Ren_eps));
+         eta = fmin(eta, (2*v4*v5 + Ren_eps)/(v4*v4 + v5*v5 + Ren_eps));
+         eta = fmin(eta, (2*v5*v6 + Ren_eps)/(v5*v5 + v6*v6 + Ren_eps));
+         const double delta = 1 - fmin(eta*Ren_irc, 1.0);
+         const double decay = pow4(1 - delta)*(1 + 4*delta);
+         const int power = min(max(int(floor(Smooth_pow - Diff_pow*(1 - decay))), 0), 13);
+         cut_off = c_p10[power];
+      } else {
+         drop();
+         cut_off = c_p10[4];
+      }
+   } else {
+      drop();
+      constexpr double Smooth_pow = 12.5, Shock_pow = 3.0, iH = 1e-1, Diff_pow = Smooth_pow - Shock_pow;
+      const double chiMax = fmax(chi1, fmax(chi2, fmax(chi3, chi4)));
+      const double theta = 1.0/(1 + chiMax*iH);
+      const int power = min(max(int(floor(Shock_pow + Diff_pow*theta)), 0), 13);
+      cut_off = c_p10[power];
+   }
+   const double a = 1.0/(a1 + a2 + a3 + a4);
+   const int b1 = (a1*a < cut_off) ? 0 : 1;
+   const int b2 = (a2*a < cut_off) ? 0 : 1;
+   const int b3 = (a3*a < cut_off) ? 0 : 1;
+   const int b4 = (a4*a < cut_off) ? 0 : 1;
+   // assemble<plus> with the side chosen at run time
+   const double y0 = plus ? y : yp1;
+   double var[4];
+   HTR_UNROLL
+   for (int k = 0; k < 4; k++) {
+      double Re[6];
+      HTR_UNROLL
+      for (int j = 0; j < 6; j++) Re[j] = plus ? c_Recon_Plus[t][6*k + j] : c_Recon_Minus[t][6*k + j];
+      var[k] = ym2*Re[0] + ym1*Re[1] + y*Re[2] + yp1*Re[3] + yp2*Re[4] + yp3*Re[5] - y0;
+   }
+   const double w1 = Co[0]*b1, w2 = Co[1]*b2, w3 = Co[2]*b3, w4 = Co[3]*b4;
+   const double w = 1.0/(w1 + w2 + w3 + w4);
+   return y0 + (w1*w)*var[0] + (w2*w)*var[1] + (w3*w)*var[2] + (w4*w)*var[3];
+}
+
 // TENO-A smoothness test used by the shock sensor: true = smooth (central flux allowed).
 // Phi is the largest Ducros value over the stencil.
 HTR_DEV bool tenoASensor(double ym2, double ym1, double y, double yp1, double yp2, double yp3, int t, double Phi) {
