@@ -76,6 +76,15 @@ __constant__ TransDerived c_tr;
 #define HTR_DEV __device__ __forceinline__
 #define HTR_UNROLL _Pragma("unroll")
 
+// a/b where 1 ulp is inside the tolerance of the production build (post-stage recovery, transport): reciprocal + multiply,
+// about half the instructions of the IEEE division sequence (the fused RK stage executed ~80 divisions per cell, ~40 % of its
+// instructions).  The strict build keeps the division: same bits as the reference's CPU code.
+#ifdef HTR_EXACT_POW
+#define HTR_QDIV(a, b) ((a)/(b))
+#else
+#define HTR_QDIV(a, b) ((a)*__drcp_rn(b))
+#endif
+
 #if !HTR_MULTICOMP
 // ------------------------------------------------------------------------------------------
 // Calorically perfect gas, one species
@@ -224,7 +233,7 @@ HTR_DEV void ClipYi(double *Yi) {
 HTR_DEV double GetMolarWeightFromYi(const double *Yi) {
    double s = 0.0;
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) s += Yi[i]/c_mix.species[i].W;
+   for (int i = 0; i < nSpec; i++) s += HTR_QDIV(Yi[i], c_mix.species[i].W);
    return 1.0/s;
 }
 HTR_DEV double GetMolarWeightFromXi(const double *Xi) {
@@ -235,11 +244,11 @@ HTR_DEV double GetMolarWeightFromXi(const double *Xi) {
 }
 HTR_DEV void GetMolarFractions(double *Xi, double MixW, const double *Yi) {
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) Xi[i] = Yi[i]*MixW/c_mix.species[i].W;
+   for (int i = 0; i < nSpec; i++) Xi[i] = HTR_QDIV(Yi[i]*MixW, c_mix.species[i].W);
 }
 HTR_DEV void GetMassFractions(double *Yi, double MixW, const double *Xi) {
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) Yi[i] = Xi[i]*c_mix.species[i].W/MixW;
+   for (int i = 0; i < nSpec; i++) Yi[i] = HTR_QDIV(Xi[i]*c_mix.species[i].W, MixW);
 }
 HTR_DEV double GetRhoFromRhoYi(const double *rhoYi) {
    double rho = 0.0;
@@ -278,7 +287,7 @@ HTR_DEV double GetInternalEnergy(double Tn, const double *Yi) {
    const double Tinv = 1.0/T, logT = log(T);
    double e = 0.0;
    HTR_UNROLL
-   for (int i = 0; i < nSpec; i++) e += Yi[i]*(spec::GetEnthalpy(c_mix.species[i], c_der[i], T, Tinv, logT) - RGAS*T/c_mix.species[i].W);
+   for (int i = 0; i < nSpec; i++) e += Yi[i]*(spec::GetEnthalpy(c_mix.species[i], c_der[i], T, Tinv, logT) - HTR_QDIV(RGAS*T, c_mix.species[i].W));
    return e*c_mix.ieRef;
 }
 // Newton iteration on e(T) = e0 from the caller's guess (step tolerance 1e-8 on non-dimensional T)
@@ -286,13 +295,13 @@ HTR_DEV double GetTFromInternalEnergy(double e0, double T, const double *Yi) {
    double dfdT = 1.0;
    for (int j = 0; j < 1000; j++) {
       const double f = e0 - GetInternalEnergy(T, Yi);
-      if (fabs(f/dfdT) < 1e-8) break;
+      if (fabs(HTR_QDIV(f, dfdT)) < 1e-8) break;
       dfdT = 0.0;
       const double Td = T*c_mix.TRef, Tdinv = 1.0/Td;
       HTR_UNROLL
       for (int i = 0; i < nSpec; i++)
          dfdT += Yi[i]*(spec::GetCp(c_mix.species[i], c_der[i], Td, Tdinv) - c_der[i].rOvW)*c_mix.iCpRef;
-      T += f/dfdT;
+      T += HTR_QDIV(f, dfdT);
    }
    return T;
 }
@@ -380,7 +389,7 @@ HTR_DEV void GetTransport(double &muOut, double &lamOut, double *Di, double Pn, 
       const double dm = 0.8662326188 + Ts*(1.3913958626 + Ts*(3.158490576 + Ts*(0.18973411754 + Ts*0.00018682962894)));
       double lami;
       if (s.diff.Geom == 0) {
-         muk[i] = c_tr.cmu[i]*sqrtT*dm/nm;
+         muk[i] = HTR_QDIV(c_tr.cmu[i]*sqrtT*dm, nm);
          lami = 15.0/4*muk[i]*c_der[i].rOvW;
       } else {
          const double nd = 6.8728271691 + Ts*(9.4122316321 + Ts*(7.7442359037 + Ts*0.23424661229));
@@ -397,13 +406,13 @@ HTR_DEV void GetTransport(double &muOut, double &lamOut, double *Di, double Pn, 
          const double F = 1 + 0.5*c_tr.pi15*rs + (2 + 0.25*PI*PI)*tmp + c_tr.pi15*tmp*rs;
          const double A = 2.5 - fV;
          const double c = 2/PI*(5./3*CvROvR + fV);
-         const double iB = F/(c_tr.zf[i] + c*F);              // 1/(Zrot + c), Zrot = zf/F
-         const double fT = 2.5*(1. - 2*CvR*A*iB/(PI*CvT));
-         const double fR = fV*(1. + 2*A*iB/PI);
-         lami = muk[i]*(fT*CvT + fR*CvR + fV*CvV)/s.W;
+         const double iB = HTR_QDIV(F, c_tr.zf[i] + c*F);              // 1/(Zrot + c), Zrot = zf/F
+         const double fT = 2.5*(1. - HTR_QDIV(2*CvR*A*iB, PI*CvT));
+         const double fR = fV*(1. + HTR_QDIV(2*A*iB, PI));
+         lami = HTR_QDIV(muk[i]*(fT*CvT + fR*CvR + fV*CvV), s.W);
       }
       a += Xi[i]*lami;
-      b += Xi[i]/lami;
+      b += HTR_QDIV(Xi[i], lami);
    }
    lamOut = 0.5*(a + 1.0/b)*c_mix.ilamRef;
    double sm[nSpec], ism[nSpec];
@@ -418,7 +427,7 @@ HTR_DEV void GetTransport(double &muOut, double &lamOut, double *Di, double Pn, 
          const double Phi = 1 + sm[i]*ism[j]*c_tr.w25[i][j];
          den += Xi[j]*(Phi*Phi*c_tr.is8[i][j]);
       }
-      mu += Xi[i]*muk[i]/den;
+      mu += HTR_QDIV(Xi[i]*muk[i], den);
    }
    muOut = mu*c_mix.imuRef;
    const double pt = P*Tinv/sqrtT;
@@ -431,7 +440,7 @@ HTR_DEV void GetTransport(double &muOut, double &lamOut, double *Di, double Pn, 
          const double Ts = T*c_tr.kboEpsij[i][j];
          const double nd = 6.8728271691 + Ts*(9.4122316321 + Ts*(7.7442359037 + Ts*0.23424661229));
          const double dd = 1.45337701568 + Ts*(5.2269794238 + Ts*(9.7108519575 + Ts*(0.46539437353 + Ts*0.00041908394781)));
-         const double invDij = c_tr.cdif[i][j]*pt*nd/dd;
+         const double invDij = HTR_QDIV(c_tr.cdif[i][j]*pt*nd, dd);
          Di[i] += Xi[j]*invDij;
          Di[j] += Xi[i]*invDij;
       }
@@ -443,7 +452,7 @@ HTR_DEV void GetTransport(double &muOut, double &lamOut, double *Di, double Pn, 
       HTR_UNROLL
       for (int j = 0; j < nSpec; j++)
          if (j != i) num += Xi[j]*c_mix.species[j].W;
-      Di[i] = num*iW/Di[i];
+      Di[i] = HTR_QDIV(num*iW, Di[i]);
    }
 }
 #endif

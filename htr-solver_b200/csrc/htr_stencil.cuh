@@ -94,6 +94,19 @@ HTR_DEV double pow12(double x) {
 #endif
 }
 
+// a/b for quotients that only feed cut-off comparisons (the chi_k = tau6/(beta_k + eps) of the TENO weights, the Ren
+// indicator).  In smooth flow tau6 is tiny (1e-20 ... 1e-40), which sends the IEEE division through its slow path
+// (__cuda_sm20_div_rn_f64_full: ncu attributed 30 % of the executed instructions of the TENO kernels to it,
+// profiles/r2_v22_*); the reciprocal of the well-scaled denominator never leaves the fast path, and the product is
+// within 1 ulp of the quotient.  The strict build keeps the division (same bits as the reference's CPU code).
+HTR_DEV double cutDiv(double a, double b) {
+#ifdef HTR_EXACT_POW
+   return a/b;
+#else
+   return a*__drcp_rn(b);
+#endif
+}
+
 constexpr double tenPow(int n) {   // 10^n by repeated multiplication, like the reference's my_10_pow
    double v = 1;
    for (int i = 0; i < (n < 0 ? -n : n); i++) v = (n < 0 ? 1.0e-1 : 1.0e1)*v;
@@ -166,10 +179,10 @@ template<int OP, bool plus>
 HTR_DEV double tenoReconstruct(double ym2, double ym1, double y, double yp1, double yp2, double yp3, int t) {
    constexpr double eps = (OP == OP_TENO) ? tenPow(-10) : (OP == OP_TENOA) ? tenPow(-8) : tenPow(-16);
    const Smoothness S = smoothness<plus>(ym2, ym1, y, yp1, yp2, yp3);
-   const double chi1 = S.tau6/(S.s1 + eps);
-   const double chi2 = S.tau6/(S.s2 + eps);
-   const double chi3 = S.tau6/(S.s3 + eps);
-   const double chi4 = S.tau6/(S.s4 + eps);
+   const double chi1 = cutDiv(S.tau6, S.s1 + eps);
+   const double chi2 = cutDiv(S.tau6, S.s2 + eps);
+   const double chi3 = cutDiv(S.tau6, S.s3 + eps);
+   const double chi4 = cutDiv(S.tau6, S.s4 + eps);
    double a1 = pow6(1 + chi1), a2 = pow6(1 + chi2), a3 = pow6(1 + chi3), a4 = pow6(1 + chi4);
    double cut_off;
    if (OP == OP_TENO) {
@@ -182,10 +195,10 @@ HTR_DEV double tenoReconstruct(double ym2, double ym1, double y, double yp1, dou
          constexpr double Ren_irc = 1.0/Ren_r_c;
          constexpr double Smooth_pow = 9.5, Shock_pow = 6.0, Diff_pow = Smooth_pow - Shock_pow;
          const double v2 = fabs(ym1 - ym2), v3 = fabs(y - ym1), v4 = fabs(yp1 - y), v5 = fabs(yp2 - yp1), v6 = fabs(yp3 - yp2);
-         double eta = fmin((2*v2*v3 + Ren_eps)/(v2*v2 + v3*v3 + Ren_eps),
-                           (2*v3*v4 + Ren_eps)/(v3*v3 + v4*v4 + Ren_eps));
-         eta = fmin(eta, (2*v4*v5 + Ren_eps)/(v4*v4 + v5*v5 + Ren_eps));
-         eta = fmin(eta, (2*v5*v6 + Ren_eps)/(v5*v5 + v6*v6 + Ren_eps));
+         double eta = fmin(cutDiv(2*v2*v3 + Ren_eps, v2*v2 + v3*v3 + Ren_eps),
+                           cutDiv(2*v3*v4 + Ren_eps, v3*v3 + v4*v4 + Ren_eps));
+         eta = fmin(eta, cutDiv(2*v4*v5 + Ren_eps, v4*v4 + v5*v5 + Ren_eps));
+         eta = fmin(eta, cutDiv(2*v5*v6 + Ren_eps, v5*v5 + v6*v6 + Ren_eps));
          const double delta = 1 - fmin(eta*Ren_irc, 1.0);
          const double decay = pow4(1 - delta)*(1 + 4*delta);
          const int power = min(max(int(floor(Smooth_pow - Diff_pow*(1 - decay))), 0), 13);
@@ -222,10 +235,10 @@ HTR_DEV double tenoReconstructRT(const bool plus, double ym2, double ym1, double
    double Co[4];
    HTR_UNROLL
    for (int k = 0; k < 4; k++) Co[k] = plus ? c_Coeffs_Plus[t][k] : c_Coeffs_Minus[t][k];
-   const double chi1 = S.tau6/(S.s1 + eps);
-   const double chi2 = S.tau6/(S.s2 + eps);
-   const double chi3 = S.tau6/(S.s3 + eps);
-   const double chi4 = S.tau6/(S.s4 + eps);
+   const double chi1 = cutDiv(S.tau6, S.s1 + eps);
+   const double chi2 = cutDiv(S.tau6, S.s2 + eps);
+   const double chi3 = cutDiv(S.tau6, S.s3 + eps);
+   const double chi4 = cutDiv(S.tau6, S.s4 + eps);
    double a1 = pow6(1 + chi1), a2 = pow6(1 + chi2), a3 = pow6(1 + chi3), a4 = pow6(1 + chi4);
    auto drop = [&]() {
       if (Co[0] < 1e-10) a1 = 0.0;
@@ -244,10 +257,10 @@ HTR_DEV double tenoReconstructRT(const bool plus, double ym2, double ym1, double
          constexpr double Ren_irc = 1.0/Ren_r_c;
          constexpr double Smooth_pow = 9.5, Shock_pow = 6.0, Diff_pow = Smooth_pow - Shock_pow;
          const double v2 = fabs(ym1 - ym2), v3 = fabs(y - ym1), v4 = fabs(yp1 - y), v5 = fabs(yp2 - yp1), v6 = fabs(yp3 - yp2);
-         double eta = fmin((2*v2*v3 + Ren_eps)/(v2*v2 + v3*v3 + Ren_eps),
-                           (2*v3*v4 + Ren_eps)/(v3*v3 + v4*v4 + Ren_eps));
-         eta = fmin(eta, (2*v4*v5 + Ren_eps)/(v4*v4 + v5*v5 + Ren_eps));
-         eta = fmin(eta, (2*v5*v6 + Ren_eps)/(v5*v5 + v6*v6 + Ren_eps));
+         double eta = fmin(cutDiv(2*v2*v3 + Ren_eps, v2*v2 + v3*v3 + Ren_eps),
+                           cutDiv(2*v3*v4 + Ren_eps, v3*v3 + v4*v4 + Ren_eps));
+         eta = fmin(eta, cutDiv(2*v4*v5 + Ren_eps, v4*v4 + v5*v5 + Ren_eps));
+         eta = fmin(eta, cutDiv(2*v5*v6 + Ren_eps, v5*v5 + v6*v6 + Ren_eps));
          const double delta = 1 - fmin(eta*Ren_irc, 1.0);
          const double decay = pow4(1 - delta)*(1 + 4*delta);
          const int power = min(max(int(floor(Smooth_pow - Diff_pow*(1 - decay))), 0), 13);
@@ -303,10 +316,10 @@ HTR_DEV bool tenoASensor(double ym2, double ym1, double y, double yp1, double yp
    }
    constexpr double eps = 1e-8, Smooth_pow = 12.5, Shock_pow = 1.0, Diff_pow = Smooth_pow - Shock_pow;
    const Smoothness S = smoothness<true>(ym2, ym1, y, yp1, yp2, yp3);
-   const double a1 = pow6(1 + S.tau6/(S.s1 + eps));
-   const double a2 = pow6(1 + S.tau6/(S.s2 + eps));
-   const double a3 = pow6(1 + S.tau6/(S.s3 + eps));
-   const double a4 = pow6(1 + S.tau6/(S.s4 + eps));
+   const double a1 = pow6(1 + cutDiv(S.tau6, S.s1 + eps));
+   const double a2 = pow6(1 + cutDiv(S.tau6, S.s2 + eps));
+   const double a3 = pow6(1 + cutDiv(S.tau6, S.s3 + eps));
+   const double a4 = pow6(1 + cutDiv(S.tau6, S.s4 + eps));
    const double a = 1.0/(a1 + a2 + a3 + a4);
    const double decay = pow12(1 - Phi)*(1 + 12*Phi);
    const int power = min(max(int(floor(Smooth_pow - Diff_pow*(1 - decay))), 0), 13);
