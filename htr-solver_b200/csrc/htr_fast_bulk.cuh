@@ -200,7 +200,7 @@ euler_xy_bulk_kernel(const rfluid f, const rbox tile, const rbox B, uint8_t *__r
    HTR_UNROLL
    for (int k = 0; k < PER; k++) {
       const int n = tid + k*NT;
-      if (n < NC) d[T::O_H + n] = (rhoE[k] + d[T::O_P + n])/d[T::O_RHO + n];
+      if (n < NC) d[T::O_H + n] = HTR_QDIV(rhoE[k] + d[T::O_P + n], d[T::O_RHO + n]);
    }
    const bool anyBad = __syncthreads_or(bad);
 

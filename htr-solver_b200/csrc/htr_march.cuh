@@ -173,7 +173,7 @@ HTR_DEV void loadZRaw(ZRaw &r, const UF &f, const int n) {
 }
 HTR_DEV void toPoint(ZPt &c, const ZRaw &r) {
    c.v[0] = r.rho; c.v[1] = r.p;
-   c.v[2] = (r.rhoE + r.p)/r.rho;
+   c.v[2] = HTR_QDIV(r.rhoE + r.p, r.rho);       // production: reciprocal + multiply (1 ulp), htr_mix.cuh
    HTR_UNROLL
    for (int i = 0; i < 3; i++) c.v[3 + i] = r.u[i];
    HTR_UNROLL

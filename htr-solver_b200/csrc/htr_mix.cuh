@@ -546,15 +546,15 @@ HTR_DEV void GetProductionRates(double *w, double rhon, double Pn, double Tn, co
    const double P = Pn*c_mix.PRef;
    const double rho = rhon*c_mix.rhoRef;
    const double logT = log(T), iT = 1.0/T;
-   const double logTRP = logT + log(RGAS/P);
+   const double logTRP = logT + log(HTR_QDIV(RGAS, P));
    double G[nSpec], C[nSpec];
    HTR_UNROLL
    for (int i = 0; i < nSpec; i++) {
       w[i] = 0.0;
-      C[i] = Yi[i]*rho/c_mix.species[i].W;
+      C[i] = HTR_QDIV(Yi[i]*rho, c_mix.species[i].W);
       G[i] = spec::GetFreeEnthalpy(c_mix.species[i], c_der[i], T, iT, logT);
    }
-   const double cM = P/(RGAS*T);
+   const double cM = HTR_QDIV(P, RGAS*T);
    HTR_UNROLL
    for (int r = 0; r < MECH_NR; r++) {
 #if HTR_NTBREAC > 0
