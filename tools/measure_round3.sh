@@ -9,14 +9,13 @@ timeout 300 python -m pytest tests/test_zz_no_alloc.py -q -m gpu > $out/pytest_n
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $out/bench_reference_air512.json 2> $out/bench_reference.err
 timeout 900 python bench.py --steps 10 --warmup 3 > $out/bench_air512.json 2> $out/bench_air512.err
 python -c "import json;d=json.load(open('$out/bench_air512.json'));print(d['ms_per_step'],d['value'],d['e2e'],d['roofline'].get('frac'),d.get('parity'),d.get('time_step'))"
-for s in 2 1; do
-  timeout 400 python bench.py --steps 5 --warmup 3 --no-cpu --opt slab=$s > $out/bench_air512_slab$s.json 2>> $out/bench_other.err
-  python -c "import json;d=json.load(open('$out/bench_air512_slab$s.json'));print('slab$s', d['ms_per_step'],d['e2e'])"
-done
+timeout 300 python tools/exp_update_chemistry.py 96 > $out/update_chemistry_timing.txt 2>&1; tail -1 $out/update_chemistry_timing.txt
+timeout 300 python tools/exp_pointwise.py > $out/pointwise.txt 2>&1
 for w in air256 air256_front air512_front air512_tanh tg512_skew tg128_hybrid tg128_teno; do
   timeout 400 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu > $out/bench_$w.json 2>> $out/bench_other.err
   python -c "import json;d=json.load(open('$out/bench_$w.json'));print('$w', d['ms_per_step'],d['roofline']['kernels_ms'])"
 done
+timeout 600 python tools/parity_report.py > $out/parity_report.txt 2>&1; tail -3 $out/parity_report.txt
 # launch list of the bench command (serialised, cold-cache: shares only)
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/launches_air512.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu > $out/ncu_launches.log 2>&1
