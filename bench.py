@@ -400,8 +400,11 @@ def run_gpu(args, rank, world, local_rank):
                       "whole_tile_one_call_ms": phase_ms(lambda: boxes([tile])),
                       "inner_cells": cells(exchanger.inner), "shell_cells": [cells(b) for b in exchanger.shells],
                       "ghost_cells": [cells(b) for b in exchanger.ghost_boxes],
-                      "how": "each phase alone on the main stream, CUDA events, mean of 5, max over ranks; in the timed step the "
-                             "exchange and the ghost recovery run on a side stream under the inner box"}
+                      "overlap": bool(exchanger.overlap),
+                      "how": "each phase alone on the main stream, CUDA events, mean of 5, max over ranks; in the timed step " +
+                             ("the exchange and the ghost recovery run on a side stream under the inner box, the shells follow"
+                              if exchanger.overlap else
+                              "the exchange and the ghost recovery run first and the block is one htr_rhs call (one remote direction)")}
         except Exception as ex:
             phases = {"error": repr(ex)[:200]}
 
@@ -517,7 +520,8 @@ def run_gpu(args, rank, world, local_rank):
             dist.all_reduce(fin, op=dist.ReduceOp.MIN)
             tms = float(t.item())
             tstep = {"ms_per_time_step": tms, "cell_time_steps_per_s": cells_rank * world / (tms * 1e-3), "finite": bool(fin.item()),
-                     "includes": "HaloExchanger.time_step: sensors + 3 x (ghost exchange, htr_rhs on inner box and shells, htr_rk_stage)"}
+                     "includes": "HaloExchanger.time_step: sensors + 3 x (ghost exchange, htr_rhs " +
+                                 ("on inner box and shells" if exchanger.overlap else "on the block in one call") + ", htr_rk_stage)"}
         except Exception as ex:
             tstep = {"error": repr(ex)[:200]}
     if rank != 0:
@@ -585,7 +589,10 @@ def run_gpu(args, rank, world, local_rank):
             "config": {"workload": name, "source": src, "mixture": cfg["type"], "scheme": scheme, "diffusion": diffusion,
                        "chemistry": chemistry, "grid_per_gpu": [n, n, n], "global_grid": list(gN), "tiles": list(tiles),
                        "smooth_fraction": smooth, "l2": "inputs larger than L2 (no flush needed)" if n >= 128 else "inputs may fit L2",
-                       "halo": "none (periodic wrap by index)" if world == 1 else "3 ghost planes, NCCL send/recv per step"},
+                       "halo": "none (periodic wrap by index)" if world == 1 else
+                               ("3 ghost planes, NCCL send/recv per step, " +
+                                ("overlapped with the inner box (shells follow)" if exchanger.overlap else
+                                 "up front, then the block in one htr_rhs call (one remote direction: see halo.py)"))},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
             "roofline": roof, "cpu_baseline": cpu, "parity": parity, "time_step": tstep, "phases": phases, "build": solver.L.htr_build_info().decode()}
     emit(json.dumps(line))

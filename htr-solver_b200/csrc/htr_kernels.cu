@@ -829,13 +829,18 @@ __global__ void __launch_bounds__(RKS_NT, HTR_RKS_MINB) rk_stage_rows_kernel(con
    Pt p0; p0.x = tile.lo[0] + x0; p0.y = tile.lo[1] + blockIdx.y; p0.z = tile.lo[2] + blockIdx.z;
    {
       const double *gCo = at<const double>(f.Conserved_old, p0), *gC = at<const double>(f.Conserved, p0), *gCt = at<const double>(f.Conserved_t, p0);
+      // global -> shared without a register stop (LDGSTS): all 3 nEq copies of a thread are in flight together; ncu had 11.6 % of
+      // the kernel's stall samples on the load-then-store form of this loop (profiles/r2_v26_hot_source_lines.txt)
       for (int e = tid; e < nc*nEq; e += RKS_NT) {
-         pool[e] = gCo[e]; pool[RKS_NT*nEq + e] = gC[e]; pool[2*RKS_NT*nEq + e] = gCt[e];
+         fast::cpAsync8(pool + e, gCo + e); fast::cpAsync8(pool + RKS_NT*nEq + e, gC + e); fast::cpAsync8(pool + 2*RKS_NT*nEq + e, gCt + e);
       }
    }
-   __syncthreads();
    const bool valid = tid < nc;
    Pt p = p0; p.x += tid;
+   double T0 = 0.0;
+   if (valid) T0 = *at<double>(f.temperature, p);            // the Newton guess: requested while the rows arrive
+   fast::cpAsyncWaitAll();
+   __syncthreads();
    const double c1 = c_rk[stage][0], c2 = c_rk[stage][1], c3 = c_rk[stage][2];
    double U[nEq], Xi[nSpec], u[3], Yi[nSpec], Di[nSpec];
    HTR_UNROLL
@@ -844,7 +849,7 @@ __global__ void __launch_bounds__(RKS_NT, HTR_RKS_MINB) rk_stage_rows_kernel(con
    __syncthreads();
    if (valid) {
       double rho, MixW, P;
-      double T = *at<double>(f.temperature, p);
+      double T = T0;
       primitivesFromConserved(U, rho, Yi, MixW, u, T, P);
       mix::GetMolarFractions(Xi, MixW, Yi);
       *at<double>(f.temperature, p) = T;

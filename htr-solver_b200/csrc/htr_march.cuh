@@ -73,6 +73,14 @@
 #ifndef HTR_MZ_MINB
 #define HTR_MZ_MINB 3
 #endif
+// unroll factor of the Euler-z march: the plane ring is rotated by register moves (110 per step, ~9 % of the kernel's instructions);
+// unrolling lets the compiler rename instead, but the copies of the step (flux + chemistry source, ~22 KB of SASS each) spill
+// 0.5-0.8 KB per thread at 168 registers: measured on B200 at 512^3 (profiles/r2_v27_*) 14.0 ms at 1, 16.3 / 16.9 / 17.2 ms at 2 / 3 / 6
+#ifndef HTR_MZ_UNROLL
+#define HTR_MZ_UNROLL 1
+#endif
+#define HTR_PRAGMA(x) _Pragma(#x)
+#define HTR_UNROLL_N(n) HTR_PRAGMA(unroll n)
 #ifndef HTR_MP_MINB
 #define HTR_MP_MINB 2
 #endif
@@ -215,7 +223,7 @@ euler_z_march_kernel(const UF f, uint8_t *__restrict__ mask, int *__restrict__ f
    ZRaw nx;                                          // plane z+3 of the next step, requested one step ahead
    loadZRaw(nx, f, HTR_ZOFF(z0 + 3));
 
-   #pragma unroll 1
+   HTR_UNROLL_N(HTR_MZ_UNROLL)
    for (int z = z0; z <= z1; z++) {
       HTR_UNROLL
       for (int k = 0; k < 5; k++) c[k] = c[k + 1];

@@ -318,11 +318,14 @@ def test_ghost_layout_block_matches_periodic_tile(cfg, scheme, chem, kw):
         halo.exchange([fb.t[k]], n, 0, (1, 1, 1), None)     # static metrics: filled once at set-up
     ex = halo.HaloExchanger(s, fb, (1, 1, 1), (0, 0, 0), 0, 1)
     ex.sensors(1.0)
-    ex.rhs(scheme, True, chem, (1.0, 0.0), 1e-3)
-    got = fb.download(["Conserved_t", "shockSensorX", "shockSensorY", "shockSensorZ"])
-    for k in ("shockSensorX", "shockSensorY", "shockSensorZ"):
-        assert np.array_equal(got[k], ref[k]), k
-    assert np.array_equal(got["Conserved_t"], ref["Conserved_t"])
+    for overlap in (True, False):      # inner box + shells under the exchange | exchange up front and the block in one call
+        ex.overlap = overlap
+        fb.t["Conserved_t"].fill_(7.0)
+        ex.rhs(scheme, True, chem, (1.0, 0.0), 1e-3)
+        got = fb.download(["Conserved_t", "shockSensorX", "shockSensorY", "shockSensorZ"])
+        for k in ("shockSensorX", "shockSensorY", "shockSensorZ"):
+            assert np.array_equal(got[k], ref[k]), k
+        assert np.array_equal(got["Conserved_t"], ref["Conserved_t"]), overlap
 
 
 @pytest.mark.parametrize("cfg,chem,kw", [(CP, False, {"front": 0.3, "stretch": 0.2}),
@@ -764,6 +767,7 @@ def test_block_time_step_matches_periodic_tile(cfg, scheme, chem, kw, variant):
     for k in ("dcsi_e", "deta_e", "dzet_e", "dcsi_d", "deta_d", "dzet_d", "dcsi_s", "deta_s", "dzet_s"):
         halo.exchange([fb.t[k]], n, 0, (1, 1, 1), None)
     ex = halo.HaloExchanger(s, fb, (1, 1, 1), (0, 0, 0), 0, 1)
+    ex.overlap = True        # the decomposed form (the default from two remote directions on); the other form is one htr_rhs call
     names = ["Conserved", "Conserved_t", "temperature", "pressure", "velocity", "MolarFracs", "rho", "mu", "lam", "Di", "SoS", "MassFracs"]
     for step in range(2):
         s.TimeStep(fl, scheme, dt, diffusion=True, chemistry=chem, vorticityScale=1.0)
