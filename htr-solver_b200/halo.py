@@ -193,6 +193,16 @@ def boundary_rects(origin, n, w=HALO):
     return inner, shells
 
 
+def overlap_default(tiles, env=None):
+    """Exchange policy of HaloExchanger.rhs: True = ghost exchange on a side stream under the inner box, shells afterwards;
+    False = exchange first, then the whole block as one htr_rhs call.  The overlap pays from two remote directions on (see
+    HaloExchanger.__init__ for the measurement); HTR_OVERLAP=0/1 in the environment forces either form."""
+    env = os.environ.get("HTR_OVERLAP") if env is None else env
+    if env not in (None, ""):
+        return env != "0"
+    return sum(1 for t in tiles if t > 1) >= 2
+
+
 class HaloExchanger:
     """Per-rank driver of one block: ghost exchange overlapped with the interior RHS."""
 
@@ -218,9 +228,7 @@ class HaloExchanger:
         # one htr_rhs call (84 launches on boxes one tile thick), the exchange + ghost recovery it hides 2.0 ms per remote
         # direction -- so with ONE remote direction the step is faster with the exchange up front and the whole block in one
         # call; from two remote directions on the overlap wins.  HTR_OVERLAP=0/1 forces either form.
-        remote = sum(1 for t in self.tiles if t > 1)
-        env = os.environ.get("HTR_OVERLAP")
-        self.overlap = (remote >= 2) if env is None else (env != "0")
+        self.overlap = overlap_default(self.tiles)
 
     # ghost planes of the state, then ghost primitives/properties (on the current stream)
     def exchange_state(self):

@@ -122,3 +122,14 @@ def test_rk_coefficients_match_the_reference():
     assert RK_C == ((1.0, 0.0, 1.0), (0.75, 0.25, 0.25), (1.0/3.0, 2.0/3.0, 2.0/3.0))
     for a, b, _ in RK_C:
         assert abs(a + b - 1.0) < 1e-15
+
+
+def test_exchange_policy_by_remote_directions():
+    """HaloExchanger overlaps the exchange with the inner box from two remote directions on; with one (or none) the exchange
+    runs first and the block is one htr_rhs call (htr-solver_b200/halo.py: overlap_default).  HTR_OVERLAP forces either."""
+    assert halo.overlap_default((1, 1, 1), env="") is False
+    assert halo.overlap_default((1, 1, 2), env="") is False
+    assert halo.overlap_default((1, 2, 2), env="") is True
+    assert halo.overlap_default((2, 2, 2), env="") is True
+    assert halo.overlap_default((1, 1, 2), env="1") is True
+    assert halo.overlap_default((2, 2, 2), env="0") is False
