@@ -232,6 +232,74 @@ def test_mixtest_ch41stmix_goldens():
         chk(o.lib.htr_oracle_species_enthalpy(i, T / 300.0) * q["eRef"], e, f"hsp[{i}]")
 
 
+@pytest.mark.skipif(not have_oracle("CH4_30SpMix"), reason="oracle/_ref not built")
+def test_mixtest_ch4_30spmix_goldens():
+    """unitTests/mixTest/mixTest.rg:215-296 (CH4_30SpMix: 30 species, 184 reactions with third bodies and fall-off,
+    T = 1500 K, P = 1 atm, a lean partially burnt methane/air composition; reference state pure O2).  Oracle only: the
+    product library of this mixture is not built yet, this pins the reference build it will be tested against."""
+    cfg = {"type": "CH4_30SpMix", "LRef": 1.0, "PRef": 101325.0, "TRef": 300.0,
+           "XiRef": {"Species": [{"Name": "O2", "MolarFrac": 1.0}]}}
+    o = Oracle("CH4_30SpMix"); o.init_mix(cfg)
+    assert o.nspec == 30
+    P, T = 101325.0, 1500.0
+    q = refs(101325.0, 300.0, 3.1998800000000e-02)
+    Y = [5.44971e-04, 1e-60, 1e-60, 2.15391e-01, 1e-60, 5.62779e-03, 2.33245e-05, 1e-60, 1e-60, 1e-60,
+         1e-60, 1e-60, 1e-60, 5.27455e-02, 1.49287e-03, 5.98395e-04, 1e-60, 6.19628e-05, 1e-60, 1e-60,
+         1.23090e-05, 1e-60, 1e-60, 1.22500e-05, 1e-60, 3.12909e-05, 1e-60, 1e-60, 1e-60, 7.23443e-01]
+    r = o.mix_eval(1.0, T / 300.0, Y)
+    tol = 1e-5      # the goldens are printed with 7 digits, the mass fractions with 6
+    def chk(got, exp, what, t=tol):
+        assert abs(got / exp - 1.0) < t, (what, got, exp)
+    EMixW = 2.739850e-02
+    EWi = [2.015680e-03, 1.007840e-03, 1.599940e-02, 3.199880e-02, 1.700724e-02, 1.801508e-02, 3.300664e-02, 3.401448e-02,
+           1.201070e-02, 1.301854e-02, 1.402638e-02, 1.402638e-02, 1.503422e-02, 1.604206e-02, 2.801010e-02, 4.400950e-02,
+           2.901794e-02, 3.002578e-02, 3.103362e-02, 3.103362e-02, 3.204146e-02, 2.603708e-02, 2.704492e-02, 2.805276e-02,
+           2.906060e-02, 3.006844e-02, 4.102864e-02, 4.203648e-02, 4.304432e-02, 2.801340e-02]
+    for i, e in enumerate(EWi):
+        chk(o.lib.htr_oracle_species_W(i), e, f"W[{i}]", 1e-6)
+    chk(r["MixW"], EMixW, "MixW")
+    EXi = [7.407618e-03, 2.718537e-59, 1.712470e-60, 1.844254e-01, 1.610990e-60, 8.559107e-03, 1.936145e-05, 8.054952e-61,
+           2.281174e-60, 2.104575e-60, 1.953355e-60, 1.953355e-60, 1.822409e-60, 9.008491e-02, 1.460273e-03, 3.725361e-04,
+           9.441918e-61, 5.654101e-05, 8.828651e-61, 8.828651e-61, 1.052537e-05, 1.052288e-60, 1.013074e-60, 1.196430e-05,
+           9.428057e-61, 2.851241e-05, 6.677896e-61, 6.517791e-61, 6.365184e-61, 7.075633e-01]
+    for i, e in enumerate(EXi):
+        chk(r["Xi"][i], e, f"Xi[{i}]")
+    chk(r["rho"] * q["rhoRef"], P * EMixW / (R * T), "rho")
+    chk(r["cp"] * q["CpRef"], 1.4689114e+03, "cp")
+    chk(r["h"] * q["eRef"], 1.2239974e+06, "h")
+    chk(r["mu"] * q["muRef"], 5.4245594e-05, "mu")
+    chk(r["lam"] * q["lamRef"], 1.1047398e-01, "lam")
+    chk(r["gamma"], 1.2603842e+00, "gamma")
+    chk(r["SoS"] * q["uRef"], 7.5744434e+02, "SoS")
+    Edif = [1.159092e-03, 1.919946e-03, 4.970050e-04, 3.137183e-04, 4.876624e-04, 4.248935e-04, 3.228673e-04, 3.206944e-04,
+            4.671199e-04, 5.315370e-04, 3.640265e-04, 3.640265e-04, 3.559047e-04, 3.673578e-04, 3.204063e-04, 2.611356e-04,
+            2.816701e-04, 2.793719e-04, 2.738767e-04, 2.738767e-04, 2.732409e-04, 2.720047e-04, 2.694003e-04, 2.693776e-04,
+            2.473667e-04, 2.453524e-04, 4.018125e-04, 2.370506e-04, 2.359528e-04, 3.184521e-04]
+    for i, e in enumerate(Edif):
+        chk(r["Di"][i] * q["DiRef"], e, f"Di[{i}]")
+    Eprod = [-2.619665e-04, 8.087741e-04, 7.719548e-05, -3.614274e-03, 2.444384e-03, -7.054158e-04, -4.116491e-02, 4.263025e-02,
+             -1.594798e-53, -3.279458e-53, 1.364118e-53, 1.622365e-05, 3.088778e-02, -2.795221e-02, -2.962706e-03, 4.701254e-03,
+             3.466765e-03, -3.706480e-03, 9.079769e-05, 9.819966e-08, -8.255164e-05, 2.713259e-05, 4.723412e-08, -3.162481e-05,
+             1.908141e-05, -4.687640e-03, -8.071670e-55, 1.316211e-54, 2.042675e-56, 0.000000e+00]
+    for i, e in enumerate(Eprod):      # fall-off, third-body and plain reactions all contribute
+        if e == 0.0:
+            assert r["w"][i] * q["wiRef"] == 0.0, i
+        else:
+            chk(r["w"][i] * q["wiRef"], e, f"w[{i}]", 2e-4)      # printed inputs (6 digits) through stiff rate expressions
+    Edpdrho = [3.310111e+06, -4.697869e+07, -3.284257e+06, 3.610331e+05, -4.207291e+04, 3.871137e+06, 1.469175e+05, 1.159114e+06,
+               -1.457004e+07, -1.130521e+07, -6.921959e+06, -7.602934e+06, -2.450997e+06, 1.092006e+06, 1.427804e+06, 2.520530e+06,
+               -1.247804e+05, 1.072735e+06, 9.971174e+04, -1.386793e+05, 1.530256e+06, -2.250267e+06, -2.952978e+06, -6.743695e+05,
+               -1.372558e+06, 3.044764e+05, -1.047489e+06, 2.804470e+05, -2.391786e+05, 4.043327e+05]
+    for i, e in enumerate(Edpdrho):
+        chk(r["dpdrhoi"][i] * q["eRef"], e, f"dpdrhoi[{i}]", 1e-4)
+    Ehsp = [1.800606e+07, 2.410888e+08, 1.715512e+07, 1.268862e+06, 4.479985e+06, -1.074720e+07, 2.033562e+06, -1.907952e+06,
+            6.175101e+07, 4.882339e+07, 3.165640e+07, 3.427167e+07, 1.419724e+07, 3.381412e+05, -2.559395e+06, -7.539517e+06,
+            3.328419e+06, -1.340443e+06, 2.331136e+06, 3.246672e+06, -3.224028e+06, 1.172948e+07, 1.434182e+07, 5.510683e+06,
+            8.117429e+06, 1.607184e+06, 6.263048e+06, 1.127859e+06, 3.089845e+06, 1.370973e+06]
+    for i, e in enumerate(Ehsp):
+        chk(o.lib.htr_oracle_species_enthalpy(i, T / 300.0) * q["eRef"], e, f"hsp[{i}]")
+
+
 @needs_cp
 def test_metrics_uniform_grid_and_tanh_fixture():
     """InitializeMetricTask through the oracle: on a uniform periodic grid all nine metrics are 1/dx to round-off
