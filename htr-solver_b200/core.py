@@ -215,6 +215,12 @@ class Fluid:
     def download(self, names=None):
         return {n: self.interior(n).cpu().numpy() for n in (names or FIELD_NAMES)}
 
+    def save_npz(self, path, names=None):
+        """Interior of the fields as one .npz file: the input of tools/compare_fields.py (the numpy restatement of the
+        reference's scripts/compare_hdf.py and of its solver-test tolerance rule; HDF5 is absent on this image)."""
+        import numpy as np
+        np.savez(path, **self.download(names))
+
 
 # Runge-Kutta coefficients RK_C[STAGE] = (old state, current state, time derivative), src/prometeo_const.rg:54-58
 RK_C = ((1.0, 0.0, 1.0), (3.0/4.0, 1.0/4.0, 1.0/4.0), (1.0/3.0, 2.0/3.0, 2.0/3.0))
