@@ -65,8 +65,16 @@ const char *htr_mixture_name(void);
 int  htr_sizeof_mix(void);        /* == sizeof(reference struct Mix) for this mixture */
 const char *htr_build_info(void); /* arch, flags */
 
-/* Library switches.  "fast" (default 1): htr_rhs uses the shared-memory staged kernels for the Hybrid and
- * SkewSymmetric schemes; 0 = issue the per-task kernels only (same results; A/B testing). */
+/* Library switches (process-wide; A/B testing and measured alternatives, same results in every setting -- bit for bit in the
+ * strict build).  Defaults in brackets:
+ *   "fast"     [1] htr_rhs uses the staged kernels for the Hybrid and SkewSymmetric schemes; 0 = the per-task kernels only
+ *   "march"    [1] bit 0: Euler-z by the register-ring march; bit 1: the fused plane march; bit 2: plane march for Euler y, x only
+ *   "dasync"   [1] diffusion tiles staged by cp.async row copies (0 = cooperative loads)
+ *   "diff3"    [0] diffusion z, y, x in one kernel        "list" [1] deferred cells from a compacted list (0 = block scan)
+ *   "coop"     [0] lane-cooperative TENO (eight lanes per face)
+ *   "bulk" / "tensor" [1] TMA row / tensor-map copies in the Euler-xy kernel
+ *   "pipeline" [1] z-slab copy/compute overlap in htr_host_rhs; "slab" [0 = 14 planes] its slab thickness in tiles of 7 planes
+ * Unknown names return HTR_EINVAL.  (No counterpart in the reference: its variants are compile-time.) */
 int  htr_set_option(const char *name, int value);
 
 /* ---- mixture (replaces Mix::Mix(const Config&) + LoadMixtureTask) ----
