@@ -79,6 +79,7 @@ template<int JD, int TJ> struct ATile {
                         O_RY = O_DI + SP*NC, O_G = O_RY + SP*NC, O_V = O_G + NG*NC, TOTAL = O_V + VL*VR;
    static constexpr size_t SMEM = sizeof(double)*TOTAL;
    static_assert(TOTAL >= nEq*NT, "flux exchange reuses the staging buffer");
+   static_assert(NC <= 2*NT, "the derivative pass covers the staged box with two cells per thread");
 };
 
 // Face between staged cells ip and iq (velocity-box cells vp, vq): the operations of diffFaceStd (htr_fast.cuh), operand
